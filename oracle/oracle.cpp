@@ -1,0 +1,941 @@
+/*
+ * oracle.cpp -- CPU restatement of the rdsd2pcm conversion hot path.  TEST INFRASTRUCTURE ONLY.
+ *
+ * This file is the parity oracle for the CUDA implementation in dsd2dxd_b200/.  Only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load it.  The
+ * product (libdsd2pcm_b200.so) never links, loads or calls anything in oracle/.
+ *
+ * PARITY UNPINNED: the reference (clone206/dsd2dxd @ 6dcfa5d, rdsd2pcm @ ddd3788) is Rust; no Rust
+ * toolchain exists in this image, its dsd_reader path dependency is absent from the mount, and it
+ * has no #[test], golden vector or expected-output fixture for this path.
+ * The oracle therefore cannot be checked against reference outputs.  What pins it instead
+ * (tests/test_oracle_kat.py): impulse fixture -> the tap table itself, idle pattern -> exactly 0.0,
+ * streaming state machines == independent numpy closed forms, DC gain, 1 kHz tone level.
+ *
+ * Every routine is a literal streaming state machine following the cited reference lines
+ * (rd/ = /root/reference/src/rdsd2pcm/src/).  Arithmetic order is the reference's: compile with
+ * -O2 -ffp-contract=off, no fast-math.
+ *
+ * One deliberate substitution: the reference draws TPDF/rectangular dither and the FPD seed from
+ * rand::thread_rng() (OS-seeded, irreproducible: SURVEY.md F5).  Here the noise comes from
+ * Philox4x32-10 keyed by (seed, channel, frame) -- the same definition the CUDA path uses -- so that
+ * dithered output can be compared exactly as well as within +-1 LSB of the undithered result.
+ */
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "ref_taps.inc"
+
+namespace {
+
+// ------------------------------------------------------------------------------------------------
+// Tap table registry (A18) -- names as in rd/filters.rs, rd/filters_lm.rs
+// ------------------------------------------------------------------------------------------------
+struct TapTable { const char* name; const double* data; int len; };
+#define ORC_ROW(NAME, LEN) {#NAME, ORC_##NAME, LEN},
+const TapTable kTables[] = {ORC_TAP_TABLE_LIST(ORC_ROW)};
+#undef ORC_ROW
+const int kNumTables = (int)(sizeof(kTables) / sizeof(kTables[0]));
+
+int table_id(const char* name) {
+    for (int i = 0; i < kNumTables; ++i)
+        if (std::strcmp(kTables[i].name, name) == 0) return i;
+    return -1;
+}
+
+size_t next_pow2(size_t x) { size_t p = 1; while (p < x) p <<= 1; return p; }
+uint8_t reverse_bits8(uint8_t b) {
+    b = (uint8_t)((b >> 4) | (b << 4));
+    b = (uint8_t)(((b & 0xCC) >> 2) | ((b & 0x33) << 2));
+    b = (uint8_t)(((b & 0xAA) >> 1) | ((b & 0x55) << 1));
+    return b;
+}
+
+// ------------------------------------------------------------------------------------------------
+// A2: select_precalc_taps  rd/byte_precalc_decimator.rs:167-262.   filter in {'D','E','C','X'}
+// ------------------------------------------------------------------------------------------------
+const char* select_precalc_taps_name(int filt, int dsd_rate, int decim) {
+    switch (decim) {
+    case 128: return (filt == 'E' && dsd_rate == 4) ? "HTAPS_DSD256_128TO1_EQ" : nullptr;
+    case 8:
+        if (dsd_rate == 1) {
+            if (filt == 'D') return "HTAPS_D2P";
+            if (filt == 'X') return "HTAPS_XLD";
+            if (filt == 'E') return "HTAPS_DSD64_8TO1_EQ";
+            return nullptr;
+        } else if (dsd_rate == 2) {
+            return filt == 'E' ? "HTAPS_DDR_8TO1_EQ" : nullptr;
+        } else if (dsd_rate == 4) {
+            return filt == 'E' ? "HTAPS_DSD256_8TO1_EQ" : nullptr;
+        }
+        return nullptr;
+    case 16:
+        if (filt == 'X') return "HTAPS_16TO1_XLD";
+        if (filt == 'E') {
+            if (dsd_rate == 1) return "HTAPS_DSD64_16TO1_EQ";
+            if (dsd_rate == 2) return "HTAPS_DDR_16TO1_EQ";
+            if (dsd_rate == 4) return "HTAPS_DSD256_16TO1_EQ";
+            return nullptr;
+        }
+        if (filt == 'C') return dsd_rate == 2 ? "HTAPS_DDR_16TO1_CHEB" : nullptr;
+        return nullptr;
+    case 32:
+        if (filt == 'X') return "HTAPS_32TO1";
+        if (filt == 'E') {
+            if (dsd_rate == 1) return "HTAPS_DSD64_32TO1_EQ";
+            if (dsd_rate == 4) return "HTAPS_DSD256_32TO1_EQ";
+            return "HTAPS_DDR_32TO1_EQ";
+        }
+        if (filt == 'C') return "HTAPS_DDR_32TO1_CHEB";
+        return nullptr;
+    case 64:
+        if (filt == 'E') {
+            if (dsd_rate == 4) return "HTAPS_DSD256_64TO1_EQ";
+            if (dsd_rate == 8) return "HTAPS_DSD512_64TO1_EQ";
+            return "HTAPS_DDR_64TO1_EQ";
+        }
+        if (filt == 'C') return "HTAPS_DDR_64TO1_CHEB";
+        return nullptr;
+    default: return nullptr;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// A3/A4: BytePrecalcDecimator  rd/byte_precalc_decimator.rs:53-163
+// ------------------------------------------------------------------------------------------------
+struct BytePrecalcDecimator {
+    std::vector<std::vector<double>> tables;
+    size_t num_tables = 0;
+    uint32_t bytes_per_out = 0;
+    std::vector<uint8_t> fifo;
+    size_t fifo_pos = 0;
+    uint64_t delay_count = 0;
+    size_t table_span = 0;
+
+    // :67-108
+    static BytePrecalcDecimator* create(const double* second_half_taps, size_t half, uint32_t decim) {
+        if (decim % 8 != 0) return nullptr;
+        if (half == 0) return nullptr;
+        auto* d = new BytePrecalcDecimator();
+        d->num_tables = (half + 7) / 8;
+        // (0..num_tables).rev().map(|t| t*8): tables[0] covers the *last* 8-tap segment
+        for (size_t ti = d->num_tables; ti-- > 0;) {
+            size_t t = ti * 8;
+            std::vector<double> tbl(256);
+            size_t nbits = std::min<size_t>(half > t ? half - t : 0, 8);
+            for (int dsd_seq = 0; dsd_seq < 256; ++dsd_seq) {
+                double acc = 0.0;
+                for (size_t bit = 0; bit < nbits; ++bit) {
+                    double sign = (double)(((dsd_seq >> bit) & 1) * 2 - 1);
+                    acc = acc + sign * second_half_taps[t + bit];
+                }
+                tbl[dsd_seq] = acc;
+            }
+            d->tables.push_back(std::move(tbl));
+        }
+        d->bytes_per_out = decim / 8;
+        d->fifo.assign(next_pow2(d->num_tables * 2 + 8), 0);
+        d->fifo_pos = 0;
+        d->delay_count = (uint64_t)((half * 2 - 1) / 2);
+        d->table_span = d->num_tables * 2 - 1;
+        return d;
+    }
+
+    // :112-162
+    size_t process_bytes(const uint8_t* bytes, size_t n, double* out, size_t out_len) {
+        if (num_tables == 0 || bytes_per_out == 0) return 0;
+        const size_t mask = fifo.size() - 1;
+        uint32_t byte_count_in_frame = 0;   // NB: local -- restarts at 0 on every call (:121)
+        size_t produced = 0;
+        for (size_t bi = 0; bi < n; ++bi) {
+            fifo[fifo_pos & mask] = bytes[bi];
+            fifo_pos = (fifo_pos + 1) & mask;
+            byte_count_in_frame += 1;
+            if (byte_count_in_frame == bytes_per_out) {
+                byte_count_in_frame = 0;
+                if (delay_count > 0) {
+                    delay_count -= 1;
+                } else if (produced < out_len) {
+                    double acc = 0.0;
+                    for (size_t i = 0; i < num_tables; ++i) {
+                        size_t idx1 = (fifo_pos - (1 + i)) & mask;
+                        size_t idx2 = (fifo_pos - (1 + (table_span - i))) & mask;
+                        uint8_t byte1 = fifo[idx1];
+                        uint8_t byte2 = fifo[idx2];
+                        acc = acc + tables[i][byte1];
+                        acc = acc + tables[i][reverse_bits8(byte2)];
+                    }
+                    out[produced] = acc;
+                    produced += 1;
+                }
+                if (produced == out_len) break;
+            }
+        }
+        return produced;
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// A7: stage-1 polyphase LUT  rd/lm_resampler.rs:847-887
+// ------------------------------------------------------------------------------------------------
+typedef std::vector<std::vector<std::vector<double>>> Stage1Lut;   // [phase][group][256]
+
+Stage1Lut build_stage1_lut_from_right_half(const double* right_half, size_t n_half, uint32_t l) {
+    std::vector<double> full(right_half, right_half + n_half);
+    std::reverse(full.begin(), full.end());
+    full.insert(full.end(), right_half, right_half + n_half);
+    std::vector<std::vector<double>> phases(l);
+    for (size_t i = 0; i < full.size(); ++i) phases[i % l].push_back(full[i]);
+    Stage1Lut out;
+    for (auto& taps : phases) {
+        size_t n = taps.size();
+        size_t groups = (n + 7) / 8;
+        std::vector<std::vector<double>> phase_lut;
+        for (size_t g = 0; g < groups; ++g) {
+            size_t base = g * 8;
+            double coeffs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            for (size_t j = 0; j < 8; ++j) if (base + j < n) coeffs[j] = taps[base + j];
+            std::vector<double> group_lut(256);
+            for (unsigned b = 0; b < 256; ++b) {
+                double sum = 0.0;
+                for (size_t j = 0; j < 8; ++j) {
+                    double sign = ((b >> j) & 1) == 1 ? 1.0 : -1.0;
+                    sum += coeffs[j] * sign;
+                }
+                group_lut[b] = sum;
+            }
+            phase_lut.push_back(std::move(group_lut));
+        }
+        out.push_back(std::move(phase_lut));
+    }
+    return out;
+}
+
+// ------------------------------------------------------------------------------------------------
+// A8: Stage1Poly  rd/lm_resampler.rs:378-641   (chunking knobs :794-832 have no numeric effect: the
+// chunked loop visits groups 0..G-1 in order with one running sum, so it is restated as that loop)
+// ------------------------------------------------------------------------------------------------
+struct Stage1Poly {
+    uint32_t l, m;
+    bool accum_mode;
+    Stage1Lut lut;
+    std::vector<uint8_t> byte_ring;
+    size_t byte_mask, wbyte = 0;
+    uint8_t rolling_byte = 0;
+    uint64_t delay_high, high_index = 0;
+    uint32_t phase1 = 0;
+    uint32_t acc = 0, phase_mod = 0;
+    uint64_t input_count = 0, input_delay;
+    bool primed = false;
+
+    Stage1Poly(const double* right_half, size_t n_half, uint32_t l_, uint32_t m_) : l(l_), m(m_) {
+        uint64_t n = (uint64_t)n_half * 2;
+        delay_high = (n - 1) / 2;
+        input_delay = (delay_high + ((uint64_t)l - 1)) / (uint64_t)l;
+        lut = build_stage1_lut_from_right_half(right_half, n_half, l);
+        size_t groups_max = 0;
+        for (auto& ph : lut) groups_max = std::max(groups_max, ph.size());
+        size_t byte_cap = std::max<size_t>(next_pow2(groups_max + 16), 32);
+        byte_ring.assign(byte_cap, 0);
+        byte_mask = byte_cap - 1;
+        accum_mode = (m == 21);
+    }
+
+    // :505-519 (ring_bits is written but never read in the reference; omitted)
+    void set_next_bit(bool is_pos) {
+        uint8_t b = is_pos ? 1 : 0;
+        rolling_byte = (uint8_t)(((rolling_byte << 1) & 0xFF) | b);
+        byte_ring[wbyte] = rolling_byte;
+        wbyte = (wbyte + 1) & byte_mask;
+    }
+
+    // :603-640
+    double sum_phase_groups(const std::vector<std::vector<double>>& phase_lut) const {
+        double sum = 0.0;
+        size_t total_groups = phase_lut.size();
+        if (total_groups == 0) return 0.0;
+        size_t bidx = (wbyte + byte_mask) & byte_mask;     // newest rolling byte (time t)
+        size_t capb = byte_mask + 1;
+        for (size_t g = 0; g < total_groups; ++g) {
+            size_t idx = (bidx + capb * 64 - (g << 3)) & byte_mask;
+            sum += phase_lut[g][byte_ring[idx]];
+        }
+        return sum;
+    }
+
+    template <class F> void push_all(uint8_t bit, F&& emit) {
+        if (accum_mode) {
+            // :567-597
+            set_next_bit(bit != 0);
+            input_count += 1;
+            acc += l;
+            while (acc >= m) {
+                acc -= m;
+                if (!primed) {
+                    if (input_count >= input_delay) {
+                        primed = true;
+                    } else {
+                        phase_mod = (phase_mod + (m % l)) % l;
+                        continue;
+                    }
+                }
+                emit(sum_phase_groups(lut[phase_mod]));
+                phase_mod = (phase_mod + (m % l)) % l;
+            }
+        } else {
+            // :527-533 + sim_high_slot :538-563
+            set_next_bit(bit != 0);
+            for (uint32_t s = 0; s < l; ++s) {
+                uint64_t idx_high = high_index;
+                high_index += 1;
+                if (!primed) {
+                    if (idx_high >= delay_high) { primed = true; phase1 = 0; }
+                    continue;
+                }
+                phase1 += 1;
+                if (phase1 != m) continue;
+                phase1 = 0;
+                size_t phase = (size_t)(idx_high % (uint64_t)l);
+                emit(sum_phase_groups(lut[phase]));
+            }
+        }
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// A9: DecimFIRSym  rd/lm_resampler.rs:645-752
+// ------------------------------------------------------------------------------------------------
+struct DecimFIRSym {
+    std::vector<double> full;
+    size_t len, half, center, decim;
+    bool has_center;
+    std::vector<double> ring;
+    size_t mask, w = 0, count = 0, next_out_t;
+
+    DecimFIRSym(const double* right_half, size_t n_half, size_t decim_) : decim(decim_) {
+        full.assign(right_half, right_half + n_half);
+        std::reverse(full.begin(), full.end());
+        full.insert(full.end(), right_half, right_half + n_half);
+        len = full.size();
+        center = (len - 1) / 2;
+        has_center = (len % 2 == 1);
+        half = has_center ? (len - 1) / 2 : len / 2;
+        size_t cap = next_pow2(len + decim);
+        ring.assign(cap, 0.0);
+        mask = cap - 1;
+        next_out_t = center;
+    }
+
+    double convolve_direct() const {
+        size_t cap = ring.size();
+        size_t newest = (w + cap - 1) & mask;
+        double total = 0.0;
+        size_t idx_front = newest;
+        size_t idx_back = (newest + cap - (len - 1)) & mask;
+        for (size_t k = 0; k < half; ++k) {
+            double c = full[k];
+            double xf = ring[idx_front];
+            double xb = ring[idx_back];
+            total += c * (xf + xb);
+            idx_front = (idx_front + cap - 1) & mask;
+            idx_back = (idx_back + 1) & mask;
+        }
+        if (has_center) {
+            size_t ic = (newest + cap - center) & mask;
+            total += full[center] * ring[ic];
+        }
+        return total;
+    }
+
+    size_t process_block(const double* input, size_t n, double* out, size_t out_len) {
+        size_t produced = 0;
+        for (size_t i = 0; i < n; ++i) {
+            ring[w] = input[i];
+            w = (w + 1) & mask;
+            size_t t = count;
+            count += 1;
+            if (t != next_out_t) continue;
+            next_out_t = next_out_t + decim;
+            double a = convolve_direct();
+            if (produced < out_len) { out[produced] = a; produced += 1; }
+        }
+        return produced;
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// A5: compute_decim_and_upsample  rd/lm_resampler.rs:911-969
+// ------------------------------------------------------------------------------------------------
+const uint32_t DSD_64_RATE = 2822400;
+
+void compute_decim_and_upsample(int in_rate, uint32_t out_rate, int* decim_ratio, uint32_t* upsample_ratio) {
+    int m;
+    if (out_rate == 96000 && in_rate == 4) m = 588;
+    else if ((out_rate == 96000 && in_rate == 2) || (out_rate == 192000 && in_rate == 4)) m = 294;
+    else if (out_rate == 96000 || out_rate == 192000 || out_rate == 384000) m = 147;
+    else {
+        uint32_t base = DSD_64_RATE * (uint32_t)in_rate;
+        if (out_rate > 0 && base % out_rate == 0) m = (int)(base / out_rate);
+        else m = 64;
+    }
+    uint32_t l;
+    if (m < 147) l = 1;
+    else if (out_rate == 384000) l = in_rate == 1 ? 20 : in_rate == 2 ? 10 : 5;
+    else if (out_rate == 192000) l = in_rate == 1 ? 10 : 5;
+    else l = 5;
+    *decim_ratio = m;
+    *upsample_ratio = l;
+}
+
+// ------------------------------------------------------------------------------------------------
+// A6/A10: LMResampler  rd/lm_resampler.rs:77-375
+// ------------------------------------------------------------------------------------------------
+struct LMResampler {
+    std::unique_ptr<Stage1Poly> s1;
+    std::unique_ptr<DecimFIRSym> p2, p3;
+    std::vector<double> s1_scratch, s2_scratch;
+
+    static const TapTable& T(const char* n) { return kTables[table_id(n)]; }
+    void set(const char* t1, uint32_t l, uint32_t m1, const char* t2, size_t d2, const char* t3, size_t d3) {
+        s1.reset(new Stage1Poly(T(t1).data, T(t1).len, l, m1));
+        p2.reset(new DecimFIRSym(T(t2).data, T(t2).len, d2));
+        if (t3) p3.reset(new DecimFIRSym(T(t3).data, T(t3).len, d3));
+    }
+
+    // :87-266 ; returns nullptr and fills err on unsupported combination
+    static LMResampler* create(uint32_t l, int m, uint32_t out_rate, std::string* err) {
+        std::unique_ptr<LMResampler> r(new LMResampler());
+        switch (m) {
+        case 588:
+            if (out_rate == 96000 && l == 5) {
+                r->set("HTAPS_DDRX10_21TO1_EQ", l, 21, "HTAPS_2_68MHZ_28TO1_EQ", 28, nullptr, 0);
+                return r.release();
+            }
+            *err = "Unsupported 588: must be out_rate=96k and L=5";
+            return nullptr;
+        case 294:
+            if (out_rate == 192000 && l == 5) {
+                r->set("HTAPS_DDRX10_21TO1_EQ", l, 21, "HTAPS_2_68MHZ_14TO1_EQ", 14, nullptr, 0);
+                return r.release();
+            }
+            r->set("HTAPS_DDRX5_14TO1_EQ", l, 14, "HTAPS_2MHZ_7TO1_EQ", 7, "HTAPS_288K_3TO1_EQ", 3);
+            return r.release();
+        case 147:
+            if (out_rate == 384000) {
+                r->set("HTAPS_DDRX10_21TO1_EQ", l, 21, "HTAPS_2_68MHZ_7TO1_EQ", 7, nullptr, 0);
+                return r.release();
+            }
+            if (out_rate == 192000) {
+                if (l == 5) {
+                    r->set("HTAPS_DDRX5_7TO_1_EQ", l, 7, "HTAPS_4MHZ_7TO1_EQ", 7, "HTAPS_576K_3TO1_EQ", 3);
+                    return r.release();
+                } else if (l == 10) {
+                    r->set("HTAPS_DSDX10_21TO1_EQ", l, 21, "HTAPS_1_34MHZ_7TO1_EQ", 7, nullptr, 0);
+                    return r.release();
+                }
+            }
+            r->set("HTAPS_DSDX5_7TO1_EQ", l, 7, "HTAPS_2MHZ_7TO1_EQ", 7, "HTAPS_288K_3TO1_EQ", 3);
+            return r.release();
+        default:
+            *err = "Unsupported L/M combination";
+            return nullptr;
+        }
+    }
+
+    // :270-374
+    size_t process_bytes_lm(const uint8_t* bytes, size_t nbytes, double* out, size_t out_len) {
+        if (!s1 || !p2) return 0;
+        size_t produced_total = 0;
+        size_t i = 0;
+        size_t y1_per_byte_ub = ((8 * (size_t)s1->l) + (size_t)s1->m - 1) / (size_t)s1->m;
+        y1_per_byte_ub = std::max<size_t>(y1_per_byte_ub, 1);
+
+        while (i < nbytes && produced_total < out_len) {
+            size_t out_budget = out_len - produced_total;
+            size_t need_s2_in, need_s1_out;
+            if (p3) { size_t s2 = out_budget * p3->decim; need_s2_in = s2; need_s1_out = s2 * p2->decim; }
+            else { need_s2_in = out_budget; need_s1_out = out_budget * p2->decim; }
+
+            size_t take_bytes = need_s1_out == 0 ? 0 : (need_s1_out + y1_per_byte_ub - 1) / y1_per_byte_ub;
+            take_bytes = std::min(take_bytes, nbytes - i);
+            if (take_bytes == 0) break;
+
+            s1_scratch.clear();
+            size_t consumed_bytes = 0;
+            for (size_t k = i; k < i + take_bytes; ++k) {
+                uint8_t b = bytes[k];
+                for (int bit = 0; bit < 8; ++bit)
+                    s1->push_all((uint8_t)((b >> bit) & 1), [&](double y1) { s1_scratch.push_back(y1); });
+                consumed_bytes += 1;
+                if (s1_scratch.size() >= need_s1_out) break;
+            }
+
+            size_t used_s1 = std::min(s1_scratch.size(), need_s1_out);
+            if (p3) {
+                size_t cap_s2 = std::max<size_t>(need_s2_in, 1);
+                if (s2_scratch.size() < cap_s2) s2_scratch.resize(cap_s2, 0.0);
+                size_t n2 = p2->process_block(s1_scratch.data(), used_s1, s2_scratch.data(), cap_s2);
+                size_t n3 = p3->process_block(s2_scratch.data(), n2, out + produced_total, out_len - produced_total);
+                produced_total += n3;
+            } else {
+                size_t n2 = p2->process_block(s1_scratch.data(), used_s1, out + produced_total, out_len - produced_total);
+                produced_total += n2;
+            }
+            i += consumed_bytes;
+        }
+        return produced_total;
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// A11: calc_frames_cap  rd/lib.rs:259-270
+// ------------------------------------------------------------------------------------------------
+size_t calc_frames_cap(size_t block_size, int decim, uint32_t upsample) {
+    size_t bits_per_chan = block_size * 8;
+    size_t d = (size_t)std::abs(decim);
+    size_t frames_max = (bits_per_chan * (size_t)upsample + (d - 1)) / d;
+    size_t lm_slack = upsample > 1 ? 16 : 0;
+    return frames_max + lm_slack;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al., SC'11) -- the repo's reproducible stand-in for thread_rng (F5).
+// counter = (frame_lo, frame_hi, channel, stream_id), key = (seed_lo, seed_hi).
+// ------------------------------------------------------------------------------------------------
+struct Philox { uint32_t v[4]; };
+Philox philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+    for (int r = 0; r < 10; ++r) {
+        uint64_t p0 = (uint64_t)M0 * c0, p1 = (uint64_t)M1 * c2;
+        uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+        uint32_t n1 = (uint32_t)p1;
+        uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+        uint32_t n3 = (uint32_t)p0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += W0; k1 += W1;
+    }
+    return Philox{{c0, c1, c2, c3}};
+}
+inline double u53(uint32_t hi, uint32_t lo) {       // [0,1) with 53 random bits, as rand's Standard f64
+    uint64_t u = ((uint64_t)hi << 32) | lo;
+    return (double)(u >> 11) * (1.0 / 9007199254740992.0);
+}
+
+// ------------------------------------------------------------------------------------------------
+// A15: Dither  rd/dither.rs:25-111
+// ------------------------------------------------------------------------------------------------
+struct Dither {
+    uint32_t fpd = 1;
+    int type;                 // 'T','R','F','X'
+    double neg_scale = 1.0, pos_scale = 1.0;
+    uint64_t seed;
+
+    Dither(int type_, uint64_t seed_, bool has_scale_db, double scale_db) : type(type_), seed(seed_) {
+        if (has_scale_db) {   // DSD2DXD_DITHERSCALE :39-49
+            neg_scale = std::pow(10.0, -scale_db / 20.0);
+            pos_scale = std::pow(10.0, scale_db / 20.0);
+        }
+        if (type == 'F') {    // init_rand :71-76 with the Philox stream (stream id 0xF9D) as the u32 source
+            uint32_t k = 0;
+            while (fpd < 16386) {
+                Philox p = philox4x32_10(k, 0, 0, 0xF9Du, (uint32_t)seed, (uint32_t)(seed >> 32));
+                fpd = p.v[0];
+                ++k;
+            }
+        }
+    }
+
+    // :86-95 ; chan/frame identify the sample for the counter-based noise
+    void process_samp(double* sample, uint32_t chan, uint64_t frame) {
+        *sample *= neg_scale;
+        switch (type) {
+        case 'T': {           // :78-84  r1 - r2, r ~ U[0,0.5]
+            Philox p = philox4x32_10((uint32_t)frame, (uint32_t)(frame >> 32), chan, 0, (uint32_t)seed, (uint32_t)(seed >> 32));
+            double r1 = u53(p.v[0], p.v[1]) * 0.5;
+            double r2 = u53(p.v[2], p.v[3]) * 0.5;
+            *sample += r1 - r2;
+            break;
+        }
+        case 'R': {           // :97-100
+            Philox p = philox4x32_10((uint32_t)frame, (uint32_t)(frame >> 32), chan, 0, (uint32_t)seed, (uint32_t)(seed >> 32));
+            *sample += u53(p.v[0], p.v[1]) - 0.5;
+            break;
+        }
+        case 'F': {           // :102-110
+            double l2 = std::floor(std::log2(std::fabs(*sample)));
+            int exponent;
+            if (std::isnan(l2)) exponent = 0;                       // Rust `as i32`: NaN -> 0, saturating
+            else if (l2 <= -2147483648.0) exponent = INT32_MIN;
+            else if (l2 >= 2147483647.0) exponent = INT32_MAX;
+            else exponent = (int)l2;
+            fpd ^= fpd << 13;
+            fpd ^= fpd >> 17;
+            fpd ^= fpd << 5;
+            int64_t e2 = (int64_t)exponent + 62;                     // i32 add; no overflow for the saturated ends used here
+            if (e2 < INT32_MIN) e2 = INT32_MIN;
+            double p2 = std::ldexp(1.0, (int)std::max<int64_t>(std::min<int64_t>(e2, 4096), -4096));   // 2.0f64.powi(n)
+            *sample += ((double)fpd) * 3.4e-36 * p2;
+            *sample = (double)(float)(*sample);
+            break;
+        }
+        default: break;
+        }
+        *sample *= pos_scale;
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// A13/A14/A16/A17: PcmWriter hot part  rd/pcm_writer.rs:288-298, 365-421, 608-705
+// ------------------------------------------------------------------------------------------------
+struct PcmWriter {
+    std::vector<double> float_data;
+    double scale_factor = 1.0;
+    size_t bits, channels_num, bytes_per_sample;
+    bool stdout_mode;
+    int32_t peak_level = 0;
+    int32_t clips = 0, last_low = 0, last_high = 0;
+    Dither dither;
+    std::vector<uint8_t> stdout_buf;
+    std::vector<std::vector<int32_t>> int_samples;     // file mode, AudioFile<i32>.samples
+    std::vector<std::vector<float>> float_samples;     // file mode, AudioFile<f32>.samples
+    std::vector<uint64_t> frames_written;              // per channel (for the counter-based dither key)
+
+    PcmWriter(size_t bits_, bool stdout_mode_, double out_vol, const Dither& d, size_t cap, size_t ch, uint32_t up)
+        : float_data(cap, 0.0), bits(bits_), channels_num(ch), stdout_mode(stdout_mode_), dither(d),
+          int_samples(ch), float_samples(ch), frames_written(ch, 0) {
+        bytes_per_sample = bits == 20 ? 3 : bits / 8;
+        stdout_buf.assign(cap * ch * bytes_per_sample, 0);
+        set_scaling(out_vol, up);
+    }
+
+    // :288-298
+    void set_scaling(double volume, uint32_t upsample_ratio) {
+        double vol_scale = std::pow(10.0, volume / 20.0);
+        if (bits != 32) scale_factor = std::ldexp(1.0, (int)bits - 1);       // 2.0f64.powi(bits-1)
+        peak_level = (int32_t)std::floor(scale_factor);
+        scale_factor *= vol_scale;
+        scale_factor *= (double)upsample_ratio;
+    }
+
+    // :658-675
+    void update_clip_stats(bool low, bool high) {
+        if (low) { if (last_low == 1) clips += 1; last_low += 1; return; }
+        last_low = 0;
+        if (high) { if (last_high == 1) clips += 1; last_high += 1; return; }
+        last_high = 0;
+    }
+    // :699-705
+    static int64_t my_round(double x) {
+        double r = x < 0.0 ? std::floor(x - 0.5) : std::floor(x + 0.5);
+        if (std::isnan(r)) return 0;                          // Rust f64 -> i64 `as`: saturating, NaN -> 0
+        if (r >= 9223372036854775807.0) return INT64_MAX;
+        if (r <= -9223372036854775808.0) return INT64_MIN;
+        return (int64_t)r;
+    }
+    // :678-696
+    int32_t quantize(double qin) {
+        int32_t value = (int32_t)(uint32_t)(uint64_t)my_round(qin);   // i64 -> i32 `as`: wrapping
+        int32_t peak = peak_level;
+        int32_t mn = -peak, mx = peak - 1;
+        if (value < mn) { update_clip_stats(true, false); return mn; }
+        if (value > mx) { update_clip_stats(false, true); return mx; }
+        update_clip_stats(false, false);
+        return value;
+    }
+    // :372-396
+    void pack_int(size_t* offset, int32_t value) {
+        if (*offset + bytes_per_sample > stdout_buf.size()) return;
+        if (bytes_per_sample == 3) {
+            int32_t v = value;
+            if (bits == 20) v = (int32_t)((uint32_t)v << 4);
+            stdout_buf[*offset] = (uint8_t)(v & 0xFF);
+            stdout_buf[*offset + 1] = (uint8_t)((v >> 8) & 0xFF);
+            stdout_buf[*offset + 2] = (uint8_t)((v >> 16) & 0xFF);
+        } else if (bytes_per_sample == 2) {
+            int16_t v = (int16_t)value;
+            stdout_buf[*offset] = (uint8_t)(v & 0xFF);
+            stdout_buf[*offset + 1] = (uint8_t)((v >> 8) & 0xFF);
+        } else return;
+        *offset += bytes_per_sample;
+    }
+    // :365-370
+    void pack_float(size_t* offset, double sample) {
+        float f = (float)sample;
+        std::memcpy(&stdout_buf[*offset], &f, 4);             // little-endian host
+        *offset += 4;
+    }
+    // :651-654
+    void scale_and_dither(double* s, size_t chan) {
+        *s *= scale_factor;
+        dither.process_samp(s, (uint32_t)chan, frames_written[chan]);
+        frames_written[chan] += 1;
+    }
+    // :608-648
+    void write_to_buffer(size_t n, size_t chan) {
+        if (stdout_mode) {
+            size_t bps = bytes_per_sample;
+            size_t pcm_pos = chan * bps;
+            for (size_t s = 0; s < n; ++s) {
+                size_t out_idx = pcm_pos;
+                double q = float_data[s];
+                scale_and_dither(&q, chan);
+                if (bits == 32) pack_float(&out_idx, q);
+                else pack_int(&out_idx, quantize(q));
+                pcm_pos += channels_num * bps;
+            }
+        } else if (bits == 32) {
+            for (size_t s = 0; s < n; ++s) {
+                double q = float_data[s];
+                scale_and_dither(&q, chan);
+                float_samples[chan].push_back((float)q);
+            }
+        } else {
+            for (size_t s = 0; s < n; ++s) {
+                double q = float_data[s];
+                scale_and_dither(&q, chan);
+                int_samples[chan].push_back(quantize(q));
+            }
+        }
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// A1 (inferred contract; dsd_reader source is absent -- SURVEY.md F2): container-order payload ->
+// per-channel, time-ordered, LSB-first byte blocks of `block_size` bytes per channel per iteration.
+//   layout 'P': planar blocks  [ch0: B bytes][ch1: B bytes]...  (DSF data chunk, raw -f P)
+//   layout 'I': byte-interleaved ch0,ch1,...                    (DFF DSD chunk, raw -f I)
+// MSB-first sources are bit-reversed per byte.  A trailing partial group is split evenly.
+// ------------------------------------------------------------------------------------------------
+struct Reader {
+    const uint8_t* raw; size_t nbytes; int channels; int layout; bool lsb_first; size_t block;
+    size_t pos = 0;
+    std::vector<std::vector<uint8_t>> chan_bufs;
+    Reader(const uint8_t* r, size_t n, int c, int lay, bool lsb, size_t b)
+        : raw(r), nbytes(n), channels(c), layout(lay), lsb_first(lsb), block(b), chan_bufs(c) {}
+    // returns read_size (0 at end)
+    size_t next() {
+        size_t remain = nbytes - pos;
+        size_t per = std::min(block, remain / (size_t)channels);
+        if (per == 0) return 0;
+        for (int c = 0; c < channels; ++c) {
+            auto& dst = chan_bufs[c];
+            dst.resize(per);
+            for (size_t i = 0; i < per; ++i) {
+                uint8_t b = layout == 'P' ? raw[pos + (size_t)c * per + i] : raw[pos + i * (size_t)channels + c];
+                dst[i] = lsb_first ? b : reverse_bits8(b);
+            }
+        }
+        pos += per * (size_t)channels;
+        return per * (size_t)channels;
+    }
+};
+
+}  // namespace
+
+// =================================================================================================
+// C ABI for ctypes (tests / bench cpu_baseline only)
+// =================================================================================================
+extern "C" {
+
+struct orc_config {
+    int dsd_rate;          // 1,2,4,8
+    uint32_t out_rate;
+    int filter;            // 'E','X','D','C'
+    int bits;              // 16,20,24,32
+    int dither;            // 'T','R','F','X'
+    double level_db;
+    int channels;
+    int layout;            // 'P' planar blocks, 'I' byte-interleaved
+    int lsb_first;
+    uint32_t block_size;   // bytes per channel per reader iteration
+    uint64_t dither_seed;
+    int has_dither_scale;  // DSD2DXD_DITHERSCALE set?
+    double dither_scale_db;
+    int stdout_mode;       // 1: OutputType::Stdout packing; 0: file mode (planar i32 / f32 samples)
+};
+
+int orc_num_tables() { return kNumTables; }
+const char* orc_table_name(int id) { return (id >= 0 && id < kNumTables) ? kTables[id].name : nullptr; }
+int orc_table_len(int id) { return (id >= 0 && id < kNumTables) ? kTables[id].len : -1; }
+const double* orc_table_data(int id) { return (id >= 0 && id < kNumTables) ? kTables[id].data : nullptr; }
+int orc_table_id(const char* name) { return table_id(name); }
+
+int orc_select_precalc_taps(int filt, int dsd_rate, int decim) {
+    const char* n = select_precalc_taps_name(filt, dsd_rate, decim);
+    return n ? table_id(n) : -1;
+}
+void orc_compute_decim_and_upsample(int in_rate, uint32_t out_rate, int* m, uint32_t* l) {
+    compute_decim_and_upsample(in_rate, out_rate, m, l);
+}
+size_t orc_calc_frames_cap(size_t block, int decim, uint32_t up) { return calc_frames_cap(block, decim, up); }
+
+void* orc_bpd_new(const double* half, size_t n, uint32_t decim) { return BytePrecalcDecimator::create(half, n, decim); }
+size_t orc_bpd_process(void* h, const uint8_t* bytes, size_t n, double* out, size_t cap) {
+    return ((BytePrecalcDecimator*)h)->process_bytes(bytes, n, out, cap);
+}
+int orc_bpd_num_tables(void* h) { return (int)((BytePrecalcDecimator*)h)->num_tables; }
+const double* orc_bpd_table(void* h, int i) { return ((BytePrecalcDecimator*)h)->tables[i].data(); }
+void orc_bpd_free(void* h) { delete (BytePrecalcDecimator*)h; }
+
+void* orc_lm_new(uint32_t l, int m, uint32_t out_rate, char* err, size_t errcap) {
+    std::string e;
+    LMResampler* r = LMResampler::create(l, m, out_rate, &e);
+    if (!r && err && errcap) { std::snprintf(err, errcap, "%s", e.c_str()); }
+    return r;
+}
+size_t orc_lm_process(void* h, const uint8_t* bytes, size_t n, double* out, size_t cap) {
+    return ((LMResampler*)h)->process_bytes_lm(bytes, n, out, cap);
+}
+void orc_lm_free(void* h) { delete (LMResampler*)h; }
+
+// Stage-level access for closed-form tests: run stage 1 alone over a byte stream.
+size_t orc_stage1_run(const char* table, uint32_t l, uint32_t m, const uint8_t* bytes, size_t n, double* out, size_t cap) {
+    int id = table_id(table);
+    if (id < 0) return 0;
+    Stage1Poly s(kTables[id].data, kTables[id].len, l, m);
+    size_t k = 0;
+    for (size_t i = 0; i < n; ++i)
+        for (int bit = 0; bit < 8; ++bit)
+            s.push_all((uint8_t)((bytes[i] >> bit) & 1), [&](double y) { if (k < cap) out[k] = y; ++k; });
+    return k;
+}
+size_t orc_decimfir_run(const char* table, size_t decim, const double* in, size_t n, double* out, size_t cap) {
+    int id = table_id(table);
+    if (id < 0) return 0;
+    DecimFIRSym d(kTables[id].data, kTables[id].len, decim);
+    return d.process_block(in, n, out, cap);
+}
+
+// Scalar pieces of the writer, for unit tests
+int64_t orc_my_round(double x) { return PcmWriter::my_round(x); }
+double orc_scale_factor(int bits, double level_db, uint32_t up) {
+    Dither d('X', 0, false, 0);
+    PcmWriter w(bits, true, level_db, d, 1, 1, up);
+    return w.scale_factor;
+}
+
+// Error strings follow rd/conversion_context.rs:155-163, rd/lm_resampler.rs:115,264, rd/pcm_writer.rs:195-214
+static int fail(char* err, size_t cap, const std::string& s) { if (err && cap) std::snprintf(err, cap, "%s", s.c_str()); return 1; }
+
+/*
+ * Whole-file conversion = Rdsd2Pcm::new + do_conversion up to (not including) the file write:
+ * delegate_new rd/lib.rs:200-255, setup_resamplers rd/conversion_context.rs:116-165,
+ * process_blocks :295-328, process_channel :376-398, track_io :331-371 (byte count only).
+ *
+ * Outputs (any may be NULL):
+ *   pcm / pcm_cap / pcm_bytes : stdout-mode interleaved packed bytes (appended per block as write_stdout does)
+ *   planar_i32 / planar_f32   : file-mode samples, channel-major, `frames_cap` per channel
+ *   f64_planar                : pre-scale decimator output per channel (float_data), `frames_cap` per channel
+ *   frames_per_chan[channels], clips
+ */
+int orc_convert(const orc_config* cfg, const uint8_t* raw, size_t nbytes,
+                uint8_t* pcm, size_t pcm_cap, size_t* pcm_bytes,
+                int32_t* planar_i32, float* planar_f32, double* f64_planar, size_t frames_cap,
+                uint64_t* frames_per_chan, int32_t* clips, char* err, size_t errcap) {
+    int decim_ratio; uint32_t up;
+    compute_decim_and_upsample(cfg->dsd_rate, cfg->out_rate, &decim_ratio, &up);
+    size_t cap = calc_frames_cap(cfg->block_size, decim_ratio, up);
+    if (!(cfg->bits == 16 || cfg->bits == 20 || cfg->bits == 24 || cfg->bits == 32))
+        return fail(err, errcap, "Unsupported bit depth");
+    Dither dither(cfg->dither, cfg->dither_seed, cfg->has_dither_scale != 0, cfg->dither_scale_db);
+    PcmWriter w((size_t)cfg->bits, cfg->stdout_mode != 0, cfg->level_db, dither, cap, (size_t)cfg->channels, up);
+
+    std::vector<std::unique_ptr<LMResampler>> lms;
+    std::vector<std::unique_ptr<BytePrecalcDecimator>> decs;
+    if (up > 1) {
+        for (int c = 0; c < cfg->channels; ++c) {
+            std::string e;
+            LMResampler* r = LMResampler::create(up, decim_ratio, cfg->out_rate, &e);
+            if (!r) return fail(err, errcap, e);
+            lms.emplace_back(r);
+        }
+    } else {
+        const char* tn = select_precalc_taps_name(cfg->filter, cfg->dsd_rate, decim_ratio);
+        if (!tn) {
+            char buf[160];
+            std::snprintf(buf, sizeof buf, "Taps not found for decimation ratio %d / filter '%c' (dsd_rate %d). ",
+                          decim_ratio, cfg->filter, cfg->dsd_rate);
+            return fail(err, errcap, buf);
+        }
+        const TapTable& t = kTables[table_id(tn)];
+        for (int c = 0; c < cfg->channels; ++c) {
+            BytePrecalcDecimator* d = BytePrecalcDecimator::create(t.data, t.len, (uint32_t)decim_ratio);
+            if (!d) return fail(err, errcap, "Precalc BytePrecalcDecimator init failed");
+            decs.emplace_back(d);
+        }
+    }
+
+    Reader reader(raw, nbytes, cfg->channels, cfg->layout, cfg->lsb_first != 0, cfg->block_size);
+    std::vector<uint64_t> frames(cfg->channels, 0);
+    size_t pcm_pos = 0;
+    while (reader.next() > 0) {
+        size_t samples_used_per_chan = 0;
+        for (int chan = 0; chan < cfg->channels; ++chan) {
+            const auto& cb = reader.chan_bufs[chan];
+            size_t n = up > 1 ? lms[chan]->process_bytes_lm(cb.data(), cb.size(), w.float_data.data(), w.float_data.size())
+                              : decs[chan]->process_bytes(cb.data(), cb.size(), w.float_data.data(), w.float_data.size());
+            samples_used_per_chan = n;
+            if (f64_planar)
+                for (size_t s = 0; s < n && frames[chan] + s < frames_cap; ++s)
+                    f64_planar[(size_t)chan * frames_cap + frames[chan] + s] = w.float_data[s];
+            w.write_to_buffer(n, (size_t)chan);
+            frames[chan] += n;
+        }
+        size_t pcm_frame_bytes = samples_used_per_chan * w.channels_num * w.bytes_per_sample;
+        if (w.stdout_mode && pcm_frame_bytes > 0 && pcm_frame_bytes <= w.stdout_buf.size()) {
+            if (pcm) {
+                size_t n = std::min(pcm_frame_bytes, pcm_cap > pcm_pos ? pcm_cap - pcm_pos : 0);
+                std::memcpy(pcm + pcm_pos, w.stdout_buf.data(), n);
+            }
+            pcm_pos += pcm_frame_bytes;
+        }
+    }
+    if (!w.stdout_mode) {
+        for (int c = 0; c < cfg->channels; ++c) {
+            if (planar_i32 && cfg->bits != 32)
+                for (size_t s = 0; s < w.int_samples[c].size() && s < frames_cap; ++s)
+                    planar_i32[(size_t)c * frames_cap + s] = w.int_samples[c][s];
+            if (planar_f32 && cfg->bits == 32)
+                for (size_t s = 0; s < w.float_samples[c].size() && s < frames_cap; ++s)
+                    planar_f32[(size_t)c * frames_cap + s] = w.float_samples[c][s];
+        }
+    }
+    if (pcm_bytes) *pcm_bytes = pcm_pos;
+    if (frames_per_chan) for (int c = 0; c < cfg->channels; ++c) frames_per_chan[c] = frames[c];
+    if (clips) *clips = w.clips;
+    return 0;
+}
+
+/*
+ * Timed CPU baseline: convert `nfiles` copies of the same payload, one file per thread (the
+ * reference's Rayon model, src/main.rs:280-300), DSP only (input resident in RAM, output kept in
+ * the writer's per-block buffer).  Returns wall seconds; <0 on error.
+ */
+double orc_bench(const orc_config* cfg, const uint8_t* raw, size_t nbytes, int nfiles, int nthreads) {
+    std::atomic<int> next(0), bad(0);
+    auto t0 = std::chrono::steady_clock::now();
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; ++t)
+        th.emplace_back([&]() {
+            for (;;) {
+                int f = next.fetch_add(1);
+                if (f >= nfiles) break;
+                size_t pb = 0; int32_t cl = 0; char e[64];
+                if (orc_convert(cfg, raw, nbytes, nullptr, 0, &pb, nullptr, nullptr, nullptr, 0, nullptr, &cl, e, sizeof e)) bad++;
+            }
+        });
+    for (auto& x : th) x.join();
+    double s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return bad.load() ? -1.0 : s;
+}
+
+}  // extern "C"
