@@ -1,0 +1,115 @@
+"""ctypes binding of libdsd2pcm_b200.so -- the C ABI declared in include/dsd2pcm_b200.h.
+
+The library is the product: CUDA kernels for sm_100a behind plain-C entry points.  This module only
+loads it and declares signatures; there is no Python or CPU implementation of the conversion, and
+nothing here touches oracle/.  Import fails loudly if the library has not been built
+(`python -c "import __graft_entry__ as g; g.build()"` or `make -C dsd2dxd_b200/csrc`).
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdsd2pcm_b200.so")
+
+OK = 0
+ERR_INVALID_ARG, ERR_TAPS_NOT_FOUND, ERR_UNSUPPORTED_LM, ERR_BIT_DEPTH = 1, 2, 3, 4
+ERR_NO_DEVICE, ERR_CUDA, ERR_NOMEM, ERR_STATE, ERR_CAPACITY = 5, 6, 7, 8, 9
+OUT_INTERLEAVED_LE, OUT_INTERLEAVED_BE, OUT_PLANAR_32 = 0, 1, 2
+
+
+class Config(C.Structure):
+    _fields_ = [
+        ("dsd_rate", C.c_int32), ("out_rate", C.c_uint32), ("filter", C.c_int32), ("bits", C.c_int32),
+        ("dither", C.c_int32), ("channels", C.c_int32), ("level_db", C.c_double), ("in_layout", C.c_int32),
+        ("lsb_first", C.c_int32), ("block_size", C.c_uint32), ("out_format", C.c_int32),
+        ("dither_seed", C.c_uint64), ("has_dither_scale", C.c_int32), ("dither_scale_db", C.c_double),
+        ("device", C.c_int32), ("keep_f64", C.c_int32),
+    ]
+
+
+class PlanInfo(C.Structure):
+    _fields_ = [
+        ("decim_ratio", C.c_int32), ("upsample_ratio", C.c_uint32), ("num_stages", C.c_int32),
+        ("stage_table", (C.c_char * 32) * 3), ("stage_half_taps", C.c_int32 * 3), ("stage_decim", C.c_int32 * 3),
+        ("scale_factor", C.c_double), ("peak_level", C.c_int32), ("bytes_per_sample", C.c_int32),
+        ("frames_cap", C.c_uint64), ("lut_bytes", C.c_uint64),
+    ]
+
+
+class Job(C.Structure):
+    _fields_ = [
+        ("d_in", C.c_void_p), ("in_bytes", C.c_uint64), ("d_out", C.c_void_p), ("out_cap_bytes", C.c_uint64),
+        ("d_f64", C.c_void_p), ("f64_stride", C.c_uint64), ("dither_seed", C.c_uint64), ("frames", C.c_uint64),
+    ]
+
+
+# every symbol include/dsd2pcm_b200.h declares
+EXPORTS = [
+    "d2p_abi_version", "d2p_strerror", "d2p_last_error", "d2p_device_count",
+    "d2p_plan", "d2p_frames_for_bytes", "d2p_tap_table", "d2p_tap_table_count", "d2p_tap_table_name",
+    "d2p_create", "d2p_destroy", "d2p_push", "d2p_finish", "d2p_frames_ready", "d2p_pull", "d2p_pull_f64", "d2p_stats",
+    "d2p_convert_host", "d2p_host_alloc", "d2p_host_free",
+    "d2p_batch_create", "d2p_batch_destroy", "d2p_batch_run", "d2p_batch_launches", "d2p_batch_stats",
+]
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: build the CUDA library first (there is no fallback path)")
+    L = C.CDLL(LIB_PATH)
+    cfgp, vp, u8p = C.POINTER(Config), C.c_void_p, C.POINTER(C.c_uint8)
+    L.d2p_abi_version.restype = C.c_int
+    L.d2p_strerror.restype = C.c_char_p
+    L.d2p_strerror.argtypes = [C.c_int]
+    L.d2p_last_error.restype = C.c_char_p
+    L.d2p_device_count.restype = C.c_int
+    L.d2p_plan.argtypes = [cfgp, C.POINTER(PlanInfo)]
+    L.d2p_frames_for_bytes.restype = C.c_uint64
+    L.d2p_frames_for_bytes.argtypes = [cfgp, C.c_uint64]
+    L.d2p_tap_table.argtypes = [C.c_char_p, C.POINTER(C.POINTER(C.c_double))]
+    L.d2p_tap_table_count.restype = C.c_int
+    L.d2p_tap_table_name.restype = C.c_char_p
+    L.d2p_tap_table_name.argtypes = [C.c_int]
+    L.d2p_create.argtypes = [cfgp, C.POINTER(vp)]
+    L.d2p_destroy.argtypes = [vp]
+    L.d2p_destroy.restype = None
+    L.d2p_push.argtypes = [vp, vp, C.c_size_t]
+    L.d2p_finish.argtypes = [vp]
+    L.d2p_frames_ready.restype = C.c_uint64
+    L.d2p_frames_ready.argtypes = [vp]
+    L.d2p_pull.argtypes = [vp, vp, C.c_size_t, C.POINTER(C.c_uint64)]
+    L.d2p_pull_f64.argtypes = [vp, C.c_int, C.POINTER(C.c_double), C.c_size_t, C.POINTER(C.c_uint64)]
+    L.d2p_stats.argtypes = [vp, C.POINTER(C.c_int64), C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+    L.d2p_convert_host.argtypes = [cfgp, vp, C.c_size_t, vp, C.c_size_t, C.POINTER(C.c_uint64),
+                                   C.POINTER(C.c_int64), C.POINTER(C.c_double)]
+    L.d2p_host_alloc.restype = vp
+    L.d2p_host_alloc.argtypes = [C.c_size_t]
+    L.d2p_host_free.argtypes = [vp]
+    L.d2p_host_free.restype = None
+    L.d2p_batch_create.argtypes = [cfgp, C.POINTER(vp)]
+    L.d2p_batch_destroy.argtypes = [vp]
+    L.d2p_batch_destroy.restype = None
+    L.d2p_batch_run.argtypes = [vp, C.POINTER(Job), C.c_int, vp]
+    L.d2p_batch_launches.restype = C.c_uint64
+    L.d2p_batch_launches.argtypes = [vp]
+    L.d2p_batch_stats.argtypes = [vp, vp, C.POINTER(C.c_int64), C.POINTER(C.c_double)]
+    _lib = L
+    return L
+
+
+class D2PError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__(message)
+        self.status = status
+
+
+def check(status):
+    if status != OK:
+        L = lib()
+        detail = L.d2p_last_error().decode() or L.d2p_strerror(status).decode()
+        raise D2PError(status, detail)

@@ -1,0 +1,757 @@
+// d2p_api.cu -- C ABI of libdsd2pcm_b200.so (include/dsd2pcm_b200.h) on top of the sm_100a kernels.
+//
+// Host-side responsibilities, all stateless with respect to the signal (every output frame is a pure
+// function of absolute input positions -- d2p_plan.h):
+//   * resolve the configuration (Plan) and keep the filter LUTs resident in HBM per device,
+//   * cut the requested frame range into tiles and describe payloads as jobs (DevJob),
+//   * streaming: keep the filter halo of already-pushed input on the device between pushes,
+//   * whole-payload: pipeline H2D / kernel / D2H over three streams,
+//   * replay the reference's clip counter over the sparse clip events the kernels report.
+// There is no CPU compute path: without a CUDA device the compute entries fail with D2P_ERR_NO_DEVICE.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <climits>
+#include <cstdio>
+#include <cstring>
+#include <deque>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/dsd2pcm_b200.h"
+#include "d2p_launch.h"
+#include "d2p_plan.h"
+
+namespace d2p {
+
+static thread_local std::string g_last_error;
+static int set_err(int st, const std::string& m) { g_last_error = m; return st; }
+static int cuda_err(cudaError_t e, const char* what) {
+    char buf[256];
+    std::snprintf(buf, sizeof buf, "%s: %s", what, cudaGetErrorString(e));
+    return set_err((e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) ? D2P_ERR_NO_DEVICE : D2P_ERR_CUDA, buf);
+}
+#define CK(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return cuda_err(e__, #call); } while (0)
+
+static const unsigned int kEventCap = 1u << 16;
+
+// ------------------------------------------------------------------------------------------------
+// DevicePlan: Plan + device-resident tables + tile geometry.  Cached per (device, config key).
+// ------------------------------------------------------------------------------------------------
+struct DevicePlan {
+    Plan plan;
+    bool lm = false;
+    double* d_lut = nullptr;
+    KParams kp;              // template: jobs / stats filled per launch
+    int threads = kMaxThreads;
+    size_t smem = 0;
+    int ctas_per_sm = 1, num_sms = 0;
+    ~DevicePlan() { if (d_lut) cudaFree(d_lut); }
+};
+
+static size_t round16(size_t x) { return (x + 15) & ~(size_t)15; }
+
+static void lutfir_geometry(const Plan& p, int TF, int* tile_stride, size_t* smem) {
+    const int C = p.cfg.channels;
+    *tile_stride = (int)round16((size_t)TF * p.bpo + 2 * p.nt + 16) + 32;
+    const size_t ostage = p.cfg.out_format == D2P_OUT_PLANAR_32 ? 0 : round16((size_t)TF * C * p.bps);
+    *smem = (size_t)p.nt * 2048 + (size_t)C * *tile_stride + ostage;
+}
+
+static void lm_geometry(const Plan& p, int TF, int* tile_stride, int* s1_cap, int* s2_cap, size_t* smem) {
+    const int C = p.cfg.channels;
+    const long long k2span = p.nstages == 3 ? (long long)(TF - 1) * p.D3 + (2 * p.h3 - 1) : (TF - 1);
+    const long long cnt1 = k2span * p.D2 + (2 * p.h2 - 1) + 1;
+    *s1_cap = (int)((cnt1 + 1) & ~1LL);
+    *s2_cap = p.nstages == 3 ? (int)((k2span + 2) & ~1LL) : 0;
+    const long long bits = cnt1 * p.m1 / p.L + 64 + p.m1;
+    *tile_stride = (int)round16((size_t)(bits / 8) + 16) + 48;
+    const size_t ostage = p.cfg.out_format == D2P_OUT_PLANAR_32 ? 0 : round16((size_t)TF * C * p.bps);
+    *smem = (size_t)p.L * p.gmax * 2048 + (size_t)(*s1_cap + *s2_cap) * 8 + (size_t)C * *tile_stride + ostage;
+}
+
+static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
+    std::string msg;
+    std::unique_ptr<DevicePlan> dp(new DevicePlan());
+    int st = make_plan(cfg, &dp->plan, &msg);
+    if (st != D2P_OK) return set_err(st, msg);
+    const Plan& p = dp->plan;
+    if (cfg.dither == D2P_DITHER_FPD)
+        return set_err(D2P_ERR_INVALID_ARG, "dither F (Airwindows float dither) is not implemented on the GPU path yet");
+    dp->lm = p.nstages > 1;
+
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return set_err(D2P_ERR_NO_DEVICE, "no CUDA device available (this library has no CPU path)");
+    if (cfg.device < 0 || cfg.device >= ndev) return set_err(D2P_ERR_INVALID_ARG, "invalid device ordinal");
+    CK(cudaSetDevice(cfg.device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, cfg.device));
+    dp->num_sms = prop.multiProcessorCount;
+
+    std::vector<double> lut;
+    if (dp->lm) build_stage1_lut(p, &lut); else build_bpd_lut(p, &lut);
+    CK(cudaMalloc(&dp->d_lut, lut.size() * sizeof(double)));
+    CK(cudaMemcpy(dp->d_lut, lut.data(), lut.size() * sizeof(double), cudaMemcpyHostToDevice));
+
+    KParams& k = dp->kp;
+    std::memset(&k, 0, sizeof k);
+    k.lut = dp->d_lut;
+    k.lut_doubles = (int)lut.size();
+    k.C = cfg.channels; k.layout = cfg.in_layout; k.lsb_first = cfg.lsb_first ? 1 : 0; k.block_size = (int)cfg.block_size;
+    k.bits = cfg.bits; k.bps = p.bps; k.out_format = cfg.out_format; k.dither = cfg.dither;
+    k.has_ds = cfg.has_dither_scale ? 1 : 0; k.peak = p.peak;
+    k.scale = p.scale; k.neg_scale = p.neg_scale; k.pos_scale = p.pos_scale;
+    k.h = p.h; k.nt = p.nt; k.bpo = p.bpo;
+    k.nstages = p.nstages; k.L = (int)p.L; k.m1 = p.m1; k.accum = p.accum ? 1 : 0; k.h1 = p.h1; k.gmax = p.gmax;
+    k.ring_mask = p.ring_cap - 1; k.e0 = p.e0;
+    k.h2 = p.h2; k.D2 = p.D2; k.h3 = p.h3; k.D3 = p.D3;
+    for (uint32_t ph = 0; ph < p.L && ph < (uint32_t)kMaxPhasesDev; ++ph) k.groups[ph] = (unsigned char)p.groups[ph];
+    if (dp->lm) {
+        std::vector<double> full;
+        build_full_taps(p.tab[1], &full);
+        for (int i = 0; i < p.h2; ++i) k.c2[i] = full[i];
+        if (p.nstages == 3) {
+            build_full_taps(p.tab[2], &full);
+            for (int i = 0; i < p.h3; ++i) k.c3[i] = full[i];
+        }
+    }
+
+    // tile geometry: the largest tile that leaves room for two CTAs per SM if the LUT allows, else one
+    const size_t budget = (size_t)kMaxSmem - 1024;
+    int best_tf = 0;
+    for (int pass = 0; pass < 2 && !best_tf; ++pass) {
+        const size_t lim = pass == 0 ? budget / 2 : budget;
+        for (int tf = dp->lm ? 512 : 1024; tf >= 64; tf >>= 1) {
+            int ts, a = 0, b = 0; size_t sm;
+            if (dp->lm) lm_geometry(p, tf, &ts, &a, &b, &sm); else lutfir_geometry(p, tf, &ts, &sm);
+            if (sm <= lim && (pass == 1 || tf >= (dp->lm ? 128 : 512))) { best_tf = tf; break; }
+        }
+    }
+    if (!best_tf) return set_err(D2P_ERR_NOMEM, "filter LUT and tiles do not fit in shared memory");
+    k.TF = best_tf;
+    if (dp->lm) lm_geometry(p, best_tf, &k.tile_stride, &k.s1_cap, &k.s2_cap, &dp->smem);
+    else lutfir_geometry(p, best_tf, &k.tile_stride, &dp->smem);
+    dp->ctas_per_sm = max_ctas_per_sm(dp->lm, dp->threads, dp->smem);
+    if (dp->ctas_per_sm < 1) return set_err(D2P_ERR_CUDA, "kernel cannot be resident with the chosen tile geometry");
+    *out = dp.release();
+    return D2P_OK;
+}
+
+static void free_device_plan(DevicePlan* dp) { delete dp; }
+
+// ------------------------------------------------------------------------------------------------
+// Launcher: uploads the job table and starts one persistent kernel over all tiles of all jobs.
+// ------------------------------------------------------------------------------------------------
+struct Launcher {
+    static const int kRing = 4;
+    DevJob* h_jobs[kRing] = {nullptr, nullptr, nullptr, nullptr};   // pinned staging ring
+    DevJob* d_jobs[kRing] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[kRing] = {nullptr, nullptr, nullptr, nullptr};
+    int cap[kRing] = {0, 0, 0, 0};
+    int next = 0;
+    DevStats* d_stats = nullptr;
+    ClipEvent* d_events = nullptr;
+    uint64_t launches = 0;
+
+    int init(bool want_events) {
+        CK(cudaMalloc(&d_stats, sizeof(DevStats)));
+        CK(cudaMemset(d_stats, 0, sizeof(DevStats)));
+        if (want_events) CK(cudaMalloc(&d_events, sizeof(ClipEvent) * kEventCap));
+        for (int i = 0; i < kRing; ++i) CK(cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming));
+        return D2P_OK;
+    }
+    void destroy() {
+        for (int i = 0; i < kRing; ++i) {
+            if (h_jobs[i]) cudaFreeHost(h_jobs[i]);
+            if (d_jobs[i]) cudaFree(d_jobs[i]);
+            if (ev[i]) cudaEventDestroy(ev[i]);
+        }
+        if (d_stats) cudaFree(d_stats);
+        if (d_events) cudaFree(d_events);
+    }
+
+    // jobs[i].tile_begin / job_id are filled here.  Asynchronous on `stream`.
+    int run(const DevicePlan& dp, std::vector<DevJob>& jobs, cudaStream_t stream) {
+        unsigned long long tiles = 0;
+        std::vector<DevJob> live;
+        for (size_t i = 0; i < jobs.size(); ++i) {
+            jobs[i].job_id = (int)i;
+            if (jobs[i].f_count <= 0) continue;
+            jobs[i].tile_begin = (unsigned int)tiles;
+            tiles += (unsigned long long)((jobs[i].f_count + dp.kp.TF - 1) / dp.kp.TF);
+            live.push_back(jobs[i]);
+        }
+        if (tiles == 0) return D2P_OK;
+        if (tiles > 0xFFFFFFF0ull) return set_err(D2P_ERR_INVALID_ARG, "too many tiles in one launch");
+        const int slot = next; next = (next + 1) % kRing;
+        CK(cudaEventSynchronize(ev[slot]));                      // staging slot free again?
+        if (cap[slot] < (int)live.size()) {
+            if (h_jobs[slot]) cudaFreeHost(h_jobs[slot]);
+            if (d_jobs[slot]) cudaFree(d_jobs[slot]);
+            cap[slot] = (int)live.size() + 16;
+            CK(cudaMallocHost(&h_jobs[slot], sizeof(DevJob) * cap[slot]));
+            CK(cudaMalloc(&d_jobs[slot], sizeof(DevJob) * cap[slot]));
+        }
+        std::memcpy(h_jobs[slot], live.data(), sizeof(DevJob) * live.size());
+        CK(cudaMemcpyAsync(d_jobs[slot], h_jobs[slot], sizeof(DevJob) * live.size(), cudaMemcpyHostToDevice, stream));
+        KParams k = dp.kp;
+        k.jobs = d_jobs[slot];
+        k.njobs = (int)live.size();
+        k.total_tiles = (unsigned int)tiles;
+        k.stats = d_stats;
+        k.events = d_events;
+        k.ev_cap = d_events ? kEventCap : 0;
+        const unsigned long long want = (unsigned long long)dp.num_sms * dp.ctas_per_sm;
+        const int grid = (int)std::min<unsigned long long>(tiles, want);
+        CK(launch_kernels(k, dp.lm, grid, dp.threads, dp.smem, stream));
+        CK(cudaEventRecord(ev[slot], stream));
+        ++launches;
+        return D2P_OK;
+    }
+};
+
+// PcmWriter::update_clip_stats (rd/pcm_writer.rs:658-675) replayed over the sparse clip events.
+// Samples are visited in the reference's order: reader block, then channel, then frame.
+struct SeqEvent { unsigned long long seq; int high; };
+static int64_t replay_clips(std::vector<SeqEvent>& ev, int64_t* last_low, int64_t* last_high, unsigned long long* last_seq,
+                            bool* have_last) {
+    std::sort(ev.begin(), ev.end(), [](const SeqEvent& a, const SeqEvent& b) { return a.seq < b.seq; });
+    int64_t clips = 0;
+    for (const SeqEvent& e : ev) {
+        if (!*have_last || e.seq != *last_seq + 1) { *last_low = 0; *last_high = 0; }   // an unclipped sample in between
+        if (!e.high) { if (*last_low == 1) ++clips; *last_low += 1; }
+        else { *last_low = 0; if (*last_high == 1) ++clips; *last_high += 1; }
+        *last_seq = e.seq; *have_last = true;
+    }
+    return clips;
+}
+
+// Position of (channel, frame) in the reference's processing order for a stream fed in block_size chunks.
+static unsigned long long seq_index(const Plan& p, int ch, long long f) {
+    const long long B = p.cfg.block_size;
+    const long long need = p.bytes_needed_for_frames(f + 1);       // frame f appears in the block containing byte need-1
+    const long long blk = (need - 1) / B;
+    const long long f_before = p.frames_for_bytes(blk * B);
+    const long long f_after = p.frames_for_bytes((blk + 1) * B);
+    return (unsigned long long)(p.cfg.channels * f_before + (long long)ch * (f_after - f_before) + (f - f_before));
+}
+
+}  // namespace d2p
+
+using namespace d2p;
+
+// ================================================================================================
+// streaming context
+// ================================================================================================
+struct OutChunk {
+    uint8_t* d_pcm = nullptr;       // packed frames (interleaved) or planar32 block
+    double* d_f64 = nullptr;
+    long long frames = 0;           // frames in the chunk
+    long long consumed = 0;         // frames already pulled
+};
+
+struct d2p_ctx {
+    DevicePlan* dp = nullptr;
+    Launcher launcher;
+    cudaStream_t stream = nullptr;
+    std::vector<uint8_t> pending;   // host bytes not yet forming a whole block group
+    uint8_t* d_in[2] = {nullptr, nullptr};
+    size_t d_in_cap[2] = {0, 0};
+    int cur = 0;
+    long long base_q = 0;           // per-channel position of d_in[cur][0]
+    long long have_q = 0;           // per-channel bytes resident/consumed so far (absolute)
+    long long frames_done = 0;      // frames launched so far
+    long long frames_pulled = 0;
+    bool finished = false;
+    std::deque<OutChunk> ready;
+    // clip replay state
+    int64_t clips = 0, last_low = 0, last_high = 0;
+    unsigned long long last_seq = 0;
+    bool have_last = false, clips_inexact = false;
+    unsigned int events_seen = 0;
+};
+
+static size_t group_bytes(const d2p_config& c) {
+    return c.in_layout == D2P_LAYOUT_PLANAR ? (size_t)c.channels * c.block_size : (size_t)c.channels;
+}
+
+static int ctx_collect_events(d2p_ctx* ctx) {
+    DevStats st;
+    CK(cudaMemcpyAsync(&st, ctx->launcher.d_stats, sizeof st, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    const unsigned int n = st.n_events;
+    if (n > kEventCap) ctx->clips_inexact = true;
+    const unsigned int take = std::min(n, kEventCap);
+    if (take) {
+        std::vector<ClipEvent> ev(take);
+        CK(cudaMemcpy(ev.data(), ctx->launcher.d_events, sizeof(ClipEvent) * take, cudaMemcpyDeviceToHost));
+        std::vector<SeqEvent> se(take);
+        for (unsigned int i = 0; i < take; ++i) {
+            se[i].seq = seq_index(ctx->dp->plan, ev[i].ch_kind & 0xFFFF, ev[i].frame);
+            se[i].high = (ev[i].ch_kind >> 16) & 1;
+        }
+        ctx->clips += replay_clips(se, &ctx->last_low, &ctx->last_high, &ctx->last_seq, &ctx->have_last);
+        CK(cudaMemsetAsync(&ctx->launcher.d_stats->n_events, 0, sizeof(unsigned int), ctx->stream));
+    }
+    return D2P_OK;
+}
+
+// Launch everything computable from the bytes now resident: [frames_done, frames_for_bytes(end_q)).
+static int ctx_process(d2p_ctx* ctx, long long end_q, long long tail_q, long long tail_len) {
+    const Plan& p = ctx->dp->plan;
+    const long long f_new = p.frames_for_bytes(end_q);
+    const long long cnt = f_new - ctx->frames_done;
+    if (cnt <= 0) return D2P_OK;
+    OutChunk oc;
+    oc.frames = cnt;
+    const size_t pcm_bytes = (size_t)cnt * p.cfg.channels * (p.cfg.out_format == D2P_OUT_PLANAR_32 ? 4 : p.bps);
+    CK(cudaMallocAsync((void**)&oc.d_pcm, pcm_bytes + 16, ctx->stream));
+    if (p.cfg.keep_f64) CK(cudaMallocAsync((void**)&oc.d_f64, (size_t)cnt * p.cfg.channels * 8, ctx->stream));
+    std::vector<DevJob> jobs(1);
+    DevJob& j = jobs[0];
+    std::memset(&j, 0, sizeof j);
+    j.in = ctx->d_in[ctx->cur];
+    j.base_q = ctx->base_q; j.end_q = end_q; j.tail_q = tail_q; j.tail_len = tail_len;
+    j.f_begin = ctx->frames_done; j.f_count = cnt;
+    j.out = oc.d_pcm; j.out_stride = cnt;
+    j.f64 = oc.d_f64; j.f64_stride = cnt;
+    j.seed = p.cfg.dither_seed;
+    int st = ctx->launcher.run(*ctx->dp, jobs, ctx->stream);
+    if (st != D2P_OK) return st;
+    ctx->frames_done = f_new;
+    ctx->ready.push_back(oc);
+    if (p.cfg.bits != 32) { st = ctx_collect_events(ctx); if (st != D2P_OK) return st; }
+    return D2P_OK;
+}
+
+// Make room for `add` more container bytes after the halo of already-consumed input.
+static int ctx_prepare_input(d2p_ctx* ctx, size_t add, uint8_t** dst) {
+    const Plan& p = ctx->dp->plan;
+    const d2p_config& c = p.cfg;
+    const bool planar = c.in_layout == D2P_LAYOUT_PLANAR;
+    const long long unit = planar ? (long long)c.block_size : 16;          // keep whole blocks (planar) / 16-byte runs
+    long long keep_from = p.first_byte_needed(ctx->frames_done);
+    keep_from = (keep_from / unit) * unit;
+    if (keep_from < ctx->base_q) keep_from = ctx->base_q;
+    if (keep_from > ctx->have_q) keep_from = (ctx->have_q / unit) * unit;
+    const size_t carry = (size_t)(ctx->have_q - keep_from) * c.channels;
+    const size_t need = carry + add + 64;
+    const int nxt = ctx->cur ^ 1;
+    if (ctx->d_in_cap[nxt] < need) {
+        if (ctx->d_in[nxt]) CK(cudaFreeAsync(ctx->d_in[nxt], ctx->stream));
+        ctx->d_in_cap[nxt] = need + need / 4;
+        CK(cudaMallocAsync((void**)&ctx->d_in[nxt], ctx->d_in_cap[nxt], ctx->stream));
+    }
+    if (carry)
+        CK(cudaMemcpyAsync(ctx->d_in[nxt], ctx->d_in[ctx->cur] + (size_t)(keep_from - ctx->base_q) * c.channels, carry,
+                           cudaMemcpyDeviceToDevice, ctx->stream));
+    ctx->cur = nxt;
+    ctx->base_q = keep_from;
+    *dst = ctx->d_in[nxt] + carry;
+    return D2P_OK;
+}
+
+extern "C" {
+
+int d2p_abi_version(void) { return D2P_ABI_VERSION; }
+
+const char* d2p_strerror(int status) {
+    switch (status) {
+    case D2P_OK: return "ok";
+    case D2P_ERR_INVALID_ARG: return "invalid argument";
+    case D2P_ERR_TAPS_NOT_FOUND: return "Taps not found for decimation ratio / filter / dsd_rate";
+    case D2P_ERR_UNSUPPORTED_LM: return "Unsupported L/M combination";
+    case D2P_ERR_BIT_DEPTH: return "Unsupported bit depth";
+    case D2P_ERR_NO_DEVICE: return "no CUDA device available (this library has no CPU path)";
+    case D2P_ERR_CUDA: return "CUDA error";
+    case D2P_ERR_NOMEM: return "out of memory";
+    case D2P_ERR_STATE: return "invalid call sequence";
+    case D2P_ERR_CAPACITY: return "output buffer too small";
+    default: return "unknown status";
+    }
+}
+const char* d2p_last_error(void) { return g_last_error.c_str(); }
+
+int d2p_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int d2p_plan(const d2p_config* cfg, d2p_plan_info* info) {
+    if (!cfg || !info) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    Plan p; std::string msg;
+    int st = make_plan(*cfg, &p, &msg);
+    if (st != D2P_OK) return set_err(st, msg);
+    std::memset(info, 0, sizeof *info);
+    info->decim_ratio = p.M; info->upsample_ratio = p.L; info->num_stages = p.nstages;
+    for (int s = 0; s < p.nstages; ++s) {
+        std::snprintf(info->stage_table[s], sizeof info->stage_table[s], "%s", p.tab[s]->name);
+        info->stage_half_taps[s] = p.tab[s]->len;
+        info->stage_decim[s] = p.sdecim[s];
+    }
+    info->scale_factor = p.scale; info->peak_level = p.peak; info->bytes_per_sample = p.bps;
+    const uint64_t bits = (uint64_t)cfg->block_size * 8, d = (uint64_t)(p.M < 0 ? -p.M : p.M);
+    info->frames_cap = (bits * p.L + (d - 1)) / d + (p.L > 1 ? 16 : 0);          // calc_frames_cap rd/lib.rs:259-270
+    info->lut_bytes = p.nstages == 1 ? (uint64_t)p.nt * 2048 : (uint64_t)p.L * p.gmax * 2048;
+    return D2P_OK;
+}
+
+uint64_t d2p_frames_for_bytes(const d2p_config* cfg, uint64_t bytes_per_channel) {
+    if (!cfg) return 0;
+    Plan p; std::string msg;
+    if (make_plan(*cfg, &p, &msg) != D2P_OK) { g_last_error = msg; return 0; }
+    return (uint64_t)p.frames_for_bytes((long long)bytes_per_channel);
+}
+
+int d2p_tap_table(const char* name, const double** data) {
+    const TapTable* t = name ? find_table(name) : nullptr;
+    if (!t) return -1;
+    if (data) *data = t->data;
+    return t->len;
+}
+int d2p_tap_table_count(void) { return table_count(); }
+const char* d2p_tap_table_name(int index) { const TapTable* t = table_at(index); return t ? t->name : nullptr; }
+
+// ---- streaming -----------------------------------------------------------------------------------
+int d2p_create(const d2p_config* cfg, d2p_ctx** out) {
+    if (!cfg || !out) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    *out = nullptr;
+    DevicePlan* dp = nullptr;
+    int st = build_device_plan(*cfg, &dp);
+    if (st != D2P_OK) return st;
+    d2p_ctx* ctx = new d2p_ctx();
+    ctx->dp = dp;
+    cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { d2p_destroy(ctx); return cuda_err(e, "cudaStreamCreate"); }
+    st = ctx->launcher.init(cfg->bits != 32);
+    if (st != D2P_OK) { d2p_destroy(ctx); return st; }
+    *out = ctx;
+    return D2P_OK;
+}
+
+void d2p_destroy(d2p_ctx* ctx) {
+    if (!ctx) return;
+    if (ctx->dp) cudaSetDevice(ctx->dp->plan.cfg.device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    for (OutChunk& oc : ctx->ready) { if (oc.d_pcm) cudaFree(oc.d_pcm); if (oc.d_f64) cudaFree(oc.d_f64); }
+    for (int i = 0; i < 2; ++i) if (ctx->d_in[i]) cudaFree(ctx->d_in[i]);
+    ctx->launcher.destroy();
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    free_device_plan(ctx->dp);
+    delete ctx;
+}
+
+int d2p_push(d2p_ctx* ctx, const uint8_t* raw, size_t nbytes) {
+    if (!ctx || (!raw && nbytes)) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    if (ctx->finished) return set_err(D2P_ERR_STATE, "push after finish");
+    if (nbytes == 0) return D2P_OK;
+    const d2p_config& c = ctx->dp->plan.cfg;
+    CK(cudaSetDevice(c.device));
+    const size_t G = group_bytes(c);
+    // whole groups available = pending + raw
+    const size_t total = ctx->pending.size() + nbytes;
+    const size_t whole = (total / G) * G;
+    if (whole == 0) { ctx->pending.insert(ctx->pending.end(), raw, raw + nbytes); return D2P_OK; }
+    uint8_t* dst = nullptr;
+    int st = ctx_prepare_input(ctx, whole, &dst);
+    if (st != D2P_OK) return st;
+    size_t from_pending = ctx->pending.size();
+    if (from_pending) CK(cudaMemcpyAsync(dst, ctx->pending.data(), from_pending, cudaMemcpyHostToDevice, ctx->stream));
+    const size_t from_raw = whole - from_pending;
+    CK(cudaMemcpyAsync(dst + from_pending, raw, from_raw, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));            // `raw` and `pending` may be reused by the caller after return
+    ctx->pending.assign(raw + from_raw, raw + nbytes);
+    ctx->have_q += (long long)(whole / c.channels);
+    return ctx_process(ctx, ctx->have_q, LLONG_MAX, 0);
+}
+
+int d2p_finish(d2p_ctx* ctx) {
+    if (!ctx) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    if (ctx->finished) return D2P_OK;
+    ctx->finished = true;
+    const d2p_config& c = ctx->dp->plan.cfg;
+    CK(cudaSetDevice(c.device));
+    const size_t per = ctx->pending.size() / c.channels;      // trailing partial group: split evenly (A1)
+    if (per == 0) return D2P_OK;
+    const size_t take = per * c.channels;
+    uint8_t* dst = nullptr;
+    int st = ctx_prepare_input(ctx, take, &dst);
+    if (st != D2P_OK) return st;
+    CK(cudaMemcpyAsync(dst, ctx->pending.data(), take, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    const long long tail_q = ctx->have_q;
+    ctx->have_q += (long long)per;
+    ctx->pending.clear();
+    if (c.in_layout == D2P_LAYOUT_PLANAR) return ctx_process(ctx, ctx->have_q, tail_q, (long long)per);
+    return ctx_process(ctx, ctx->have_q, LLONG_MAX, 0);
+}
+
+uint64_t d2p_frames_ready(const d2p_ctx* ctx) { return ctx ? (uint64_t)(ctx->frames_done - ctx->frames_pulled) : 0; }
+
+int d2p_pull(d2p_ctx* ctx, void* pcm, size_t cap_bytes, uint64_t* frames) {
+    if (!ctx || !pcm || !frames) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    const Plan& p = ctx->dp->plan;
+    const d2p_config& c = p.cfg;
+    CK(cudaSetDevice(c.device));
+    *frames = 0;
+    if (c.out_format == D2P_OUT_PLANAR_32) {
+        // channel-major result: all ready chunks are merged, `n` frames per channel
+        const uint64_t avail = d2p_frames_ready(ctx);
+        const uint64_t n = std::min<uint64_t>(avail, cap_bytes / ((size_t)c.channels * 4));
+        if (n == 0) return D2P_OK;
+        uint64_t done = 0;
+        while (done < n) {
+            OutChunk& oc = ctx->ready.front();
+            const uint64_t take = std::min<uint64_t>(n - done, (uint64_t)(oc.frames - oc.consumed));
+            for (int ch = 0; ch < c.channels; ++ch)
+                CK(cudaMemcpyAsync((uint8_t*)pcm + ((size_t)ch * n + done) * 4,
+                                   oc.d_pcm + ((size_t)ch * oc.frames + oc.consumed) * 4, take * 4,
+                                   cudaMemcpyDeviceToHost, ctx->stream));
+            oc.consumed += (long long)take;
+            done += take;
+            if (oc.consumed == oc.frames) {
+                CK(cudaStreamSynchronize(ctx->stream));
+                cudaFreeAsync(oc.d_pcm, ctx->stream);
+                if (oc.d_f64) cudaFreeAsync(oc.d_f64, ctx->stream);
+                ctx->ready.pop_front();
+            }
+        }
+        CK(cudaStreamSynchronize(ctx->stream));
+        ctx->frames_pulled += (long long)n;
+        *frames = n;
+        return D2P_OK;
+    }
+    const size_t fb = (size_t)c.channels * p.bps;
+    uint64_t room = cap_bytes / fb, done = 0;
+    while (room && !ctx->ready.empty()) {
+        OutChunk& oc = ctx->ready.front();
+        const uint64_t take = std::min<uint64_t>(room, (uint64_t)(oc.frames - oc.consumed));
+        CK(cudaMemcpyAsync((uint8_t*)pcm + done * fb, oc.d_pcm + (size_t)oc.consumed * fb, take * fb,
+                           cudaMemcpyDeviceToHost, ctx->stream));
+        oc.consumed += (long long)take; done += take; room -= take;
+        if (oc.consumed == oc.frames) {
+            CK(cudaStreamSynchronize(ctx->stream));
+            cudaFreeAsync(oc.d_pcm, ctx->stream);
+            if (oc.d_f64) cudaFreeAsync(oc.d_f64, ctx->stream);
+            ctx->ready.pop_front();
+        }
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->frames_pulled += (long long)done;
+    *frames = done;
+    return D2P_OK;
+}
+
+int d2p_pull_f64(d2p_ctx* ctx, int chan, double* out, size_t cap, uint64_t* n) {
+    if (!ctx || !out || !n) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    const d2p_config& c = ctx->dp->plan.cfg;
+    if (!c.keep_f64) return set_err(D2P_ERR_STATE, "context was created without keep_f64");
+    if (chan < 0 || chan >= c.channels) return set_err(D2P_ERR_INVALID_ARG, "bad channel");
+    CK(cudaSetDevice(c.device));
+    uint64_t done = 0;
+    for (const OutChunk& oc : ctx->ready) {
+        if (done >= cap) break;
+        const uint64_t take = std::min<uint64_t>(cap - done, (uint64_t)(oc.frames - oc.consumed));
+        CK(cudaMemcpyAsync(out + done, oc.d_f64 + (size_t)chan * oc.frames + oc.consumed, take * 8,
+                           cudaMemcpyDeviceToHost, ctx->stream));
+        done += take;
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    *n = done;
+    return D2P_OK;
+}
+
+int d2p_stats(d2p_ctx* ctx, int64_t* clips, double* peak_abs, int64_t* clipped_samples) {
+    if (!ctx) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    CK(cudaSetDevice(ctx->dp->plan.cfg.device));
+    DevStats st;
+    CK(cudaMemcpyAsync(&st, ctx->launcher.d_stats, sizeof st, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (clips) *clips = ctx->clips_inexact ? -1 : ctx->clips;
+    if (peak_abs) { double d; std::memcpy(&d, &st.peak_bits, 8); *peak_abs = d; }
+    if (clipped_samples) *clipped_samples = (int64_t)(st.clip_lo + st.clip_hi);
+    return D2P_OK;
+}
+
+// ---- pinned host memory ----------------------------------------------------------------------------
+void* d2p_host_alloc(size_t nbytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, nbytes) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void d2p_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+// ---- whole payload, host buffers, pipelined ---------------------------------------------------------
+int d2p_convert_host(const d2p_config* cfg, const uint8_t* raw, size_t nbytes, void* pcm, size_t out_cap_bytes,
+                     uint64_t* frames, int64_t* clips, double* peak_abs) {
+    if (!cfg || (!raw && nbytes) || !pcm || !frames) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    if (cfg->out_format == D2P_OUT_PLANAR_32 || cfg->keep_f64)
+        return set_err(D2P_ERR_INVALID_ARG, "d2p_convert_host produces interleaved packed PCM only");
+    DevicePlan* dp = nullptr;
+    int st = build_device_plan(*cfg, &dp);
+    if (st != D2P_OK) return st;
+    const Plan& p = dp->plan;
+    const d2p_config& c = p.cfg;
+    const bool planar = c.in_layout == D2P_LAYOUT_PLANAR;
+    const size_t G = group_bytes(c);
+    const long long unit = planar ? (long long)c.block_size : 1;          // per-channel bytes per group
+    const long long groups = (long long)(nbytes / G);
+    const long long tail_per = (long long)((nbytes - (size_t)groups * G) / c.channels);
+    const long long total_q = groups * unit + tail_per;
+    const long long total_frames = p.frames_for_bytes(total_q);
+    const size_t fb = (size_t)c.channels * p.bps;
+    *frames = 0;
+    if ((size_t)total_frames * fb > out_cap_bytes) { free_device_plan(dp); return set_err(D2P_ERR_CAPACITY, "output buffer too small"); }
+
+    const int NS = 3;
+    const long long chunk_groups = std::max<long long>(1, (long long)((64u << 20) / G));   // ~64 MiB of payload per chunk
+    cudaStream_t streams[NS]; uint8_t* d_in[NS] = {nullptr, nullptr, nullptr}; uint8_t* d_out[NS] = {nullptr, nullptr, nullptr};
+    size_t in_cap = 0, out_cap = 0;
+    Launcher launcher;
+    int rc = D2P_OK;
+    auto cleanup = [&]() {
+        for (int s = 0; s < NS; ++s) { if (streams[s]) { cudaStreamSynchronize(streams[s]); cudaStreamDestroy(streams[s]); }
+                                       if (d_in[s]) cudaFree(d_in[s]); if (d_out[s]) cudaFree(d_out[s]); }
+        launcher.destroy();
+        free_device_plan(dp);
+    };
+    for (int s = 0; s < NS; ++s) streams[s] = nullptr;
+    for (int s = 0; s < NS; ++s) if (cudaStreamCreateWithFlags(&streams[s], cudaStreamNonBlocking) != cudaSuccess) { cleanup(); return set_err(D2P_ERR_CUDA, "stream create"); }
+    if ((rc = launcher.init(false)) != D2P_OK) { cleanup(); return rc; }
+
+    // worst-case chunk footprint: chunk + halo groups (+ ragged tail on the last one)
+    const long long max_halo_q = 4096 + 2LL * p.nt + 64;                  // bytes per channel; generous for every topology
+    const long long halo_groups_max = (max_halo_q + unit - 1) / unit + 1;
+    in_cap = (size_t)(chunk_groups + halo_groups_max) * G + (size_t)tail_per * c.channels + 256;
+    {
+        const long long per_chunk_q = chunk_groups * unit + tail_per;
+        const long long fmax = p.frames_for_bytes(per_chunk_q + max_halo_q) + 64;
+        out_cap = (size_t)fmax * fb + 256;
+    }
+    for (int s = 0; s < NS; ++s) {
+        if (cudaMalloc(&d_in[s], in_cap) != cudaSuccess || cudaMalloc(&d_out[s], out_cap) != cudaSuccess) { cleanup(); return set_err(D2P_ERR_NOMEM, "device allocation failed"); }
+    }
+
+    long long f_done = 0;
+    int ci = 0;
+    for (long long g0 = 0;;) {
+        const long long g1 = std::min(groups, g0 + chunk_groups);
+        const bool last = g1 >= groups;
+        const long long end_q = g1 * unit + (last ? tail_per : 0);
+        const long long f_new = p.frames_for_bytes(end_q);
+        if (f_new > f_done) {
+            const int s = ci % NS; ++ci;
+            long long keep_q = p.first_byte_needed(f_done);
+            long long gk = keep_q / unit;                                  // first group to ship
+            if (!planar) gk = (gk / 16) * 16;                              // keep interleaved chunks 16-aligned per channel
+            const size_t off = (size_t)gk * G;
+            const size_t len = (size_t)(g1 - gk) * G + (last ? (size_t)tail_per * c.channels : 0);
+            if (len > in_cap) { rc = set_err(D2P_ERR_NOMEM, "internal: chunk larger than staging buffer"); break; }
+            if (cudaMemcpyAsync(d_in[s], raw + off, len, cudaMemcpyHostToDevice, streams[s]) != cudaSuccess) { rc = cuda_err(cudaGetLastError(), "H2D"); break; }
+            std::vector<DevJob> jobs(1);
+            DevJob& j = jobs[0];
+            std::memset(&j, 0, sizeof j);
+            j.in = d_in[s]; j.base_q = gk * unit; j.end_q = end_q;
+            j.tail_q = (last && tail_per > 0 && planar) ? groups * unit : LLONG_MAX; j.tail_len = tail_per;
+            j.f_begin = f_done; j.f_count = f_new - f_done;
+            j.out = d_out[s]; j.seed = c.dither_seed;
+            if ((size_t)j.f_count * fb > out_cap) { rc = set_err(D2P_ERR_NOMEM, "internal: chunk output larger than staging buffer"); break; }
+            if ((rc = launcher.run(*dp, jobs, streams[s])) != D2P_OK) break;
+            if (cudaMemcpyAsync((uint8_t*)pcm + (size_t)f_done * fb, d_out[s], (size_t)j.f_count * fb, cudaMemcpyDeviceToHost, streams[s]) != cudaSuccess) { rc = cuda_err(cudaGetLastError(), "D2H"); break; }
+            f_done = f_new;
+        }
+        if (last) break;
+        g0 = g1;
+    }
+    for (int s = 0; s < NS; ++s) if (streams[s]) { cudaError_t e = cudaStreamSynchronize(streams[s]); if (e != cudaSuccess && rc == D2P_OK) rc = cuda_err(e, "stream sync"); }
+    if (rc == D2P_OK) {
+        DevStats stt;
+        if (cudaMemcpy(&stt, launcher.d_stats, sizeof stt, cudaMemcpyDeviceToHost) == cudaSuccess) {
+            if (clips) *clips = (int64_t)(stt.clip_lo + stt.clip_hi);      // plain count here; exact replay is the streaming ctx's job
+            if (peak_abs) { double d; std::memcpy(&d, &stt.peak_bits, 8); *peak_abs = d; }
+        }
+        *frames = (uint64_t)f_done;
+    }
+    cleanup();
+    return rc;
+}
+
+// ---- device-resident batch --------------------------------------------------------------------------
+struct d2p_batch {
+    DevicePlan* dp = nullptr;
+    Launcher launcher;
+};
+
+int d2p_batch_create(const d2p_config* cfg, d2p_batch** out) {
+    if (!cfg || !out) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    *out = nullptr;
+    DevicePlan* dp = nullptr;
+    int st = build_device_plan(*cfg, &dp);
+    if (st != D2P_OK) return st;
+    d2p_batch* b = new d2p_batch();
+    b->dp = dp;
+    st = b->launcher.init(false);
+    if (st != D2P_OK) { d2p_batch_destroy(b); return st; }
+    *out = b;
+    return D2P_OK;
+}
+
+void d2p_batch_destroy(d2p_batch* b) {
+    if (!b) return;
+    if (b->dp) cudaSetDevice(b->dp->plan.cfg.device);
+    cudaDeviceSynchronize();
+    b->launcher.destroy();
+    free_device_plan(b->dp);
+    delete b;
+}
+
+int d2p_batch_run(d2p_batch* b, d2p_job* jobs, int njobs, void* cuda_stream) {
+    if (!b || (!jobs && njobs)) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    const Plan& p = b->dp->plan;
+    const d2p_config& c = p.cfg;
+    CK(cudaSetDevice(c.device));
+    const bool planar = c.in_layout == D2P_LAYOUT_PLANAR;
+    const size_t G = group_bytes(c);
+    const long long unit = planar ? (long long)c.block_size : 1;
+    const size_t fb = (size_t)c.channels * (c.out_format == D2P_OUT_PLANAR_32 ? 4 : p.bps);
+    std::vector<DevJob> dj((size_t)njobs);
+    for (int i = 0; i < njobs; ++i) {
+        d2p_job& u = jobs[i];
+        const long long groups = (long long)(u.in_bytes / G);
+        const long long tail_per = (long long)((u.in_bytes - (size_t)groups * G) / c.channels);
+        const long long total_q = groups * unit + tail_per;
+        const long long nf = p.frames_for_bytes(total_q);
+        if ((size_t)nf * fb > u.out_cap_bytes) return set_err(D2P_ERR_CAPACITY, "job output buffer too small");
+        if (u.d_f64 && (long long)u.f64_stride < nf) return set_err(D2P_ERR_CAPACITY, "job f64 stride too small");
+        DevJob& j = dj[i];
+        std::memset(&j, 0, sizeof j);
+        j.in = (const uint8_t*)u.d_in; j.base_q = 0; j.end_q = total_q;
+        j.tail_q = (planar && tail_per > 0) ? groups * unit : LLONG_MAX; j.tail_len = tail_per;
+        j.f_begin = 0; j.f_count = nf;
+        j.out = (uint8_t*)u.d_out; j.out_stride = nf;
+        j.f64 = u.d_f64; j.f64_stride = (long long)u.f64_stride;
+        j.seed = u.dither_seed;
+        u.frames = (uint64_t)nf;
+    }
+    return b->launcher.run(*b->dp, dj, (cudaStream_t)cuda_stream);
+}
+
+uint64_t d2p_batch_launches(const d2p_batch* b) { return b ? b->launcher.launches : 0; }
+
+int d2p_batch_stats(d2p_batch* b, void* cuda_stream, int64_t* clipped_samples, double* peak_abs) {
+    if (!b) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    CK(cudaSetDevice(b->dp->plan.cfg.device));
+    DevStats st;
+    CK(cudaMemcpyAsync(&st, b->launcher.d_stats, sizeof st, cudaMemcpyDeviceToHost, (cudaStream_t)cuda_stream));
+    CK(cudaStreamSynchronize((cudaStream_t)cuda_stream));
+    if (clipped_samples) *clipped_samples = (int64_t)(st.clip_lo + st.clip_hi);
+    if (peak_abs) { double d; std::memcpy(&d, &st.peak_bits, 8); *peak_abs = d; }
+    return D2P_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,72 @@
+// d2p_device.h -- structures shared between the host launcher and the sm_100a kernels.
+#pragma once
+#include <cstdint>
+
+namespace d2p {
+
+// One contiguous run of output frames of one input payload ("file").  All positions are absolute
+// per-channel stream positions, so a job can describe a whole file or one streamed block with halo.
+struct DevJob {
+    const uint8_t* in;        // container-order bytes; byte 0 of the buffer is per-channel position base_q
+    long long base_q;         // per-channel byte index of the first byte held in `in` (block-group aligned)
+    long long end_q;          // per-channel bytes of the stream available (absolute)
+    long long tail_q;         // planar only: position where a ragged final block group starts (else LLONG_MAX)
+    long long tail_len;       // per-channel bytes of that group (each channel's run is tail_len long)
+    long long f_begin;        // first absolute frame to produce
+    long long f_count;        // frames to produce
+    uint8_t* out;             // interleaved: where frame f_begin goes; planar32: channel 0 / frame f_begin
+    long long out_stride;     // planar32: elements between channels
+    double* f64;              // optional pre-scale output, channel-major, frame f_begin at index 0
+    long long f64_stride;
+    unsigned long long seed;  // dither key
+    unsigned int tile_begin;  // first global tile index of this job
+    int job_id;
+};
+
+struct DevStats {
+    unsigned long long peak_bits;   // max |sample * scale| as f64 bits (non-negative doubles order as integers)
+    unsigned long long clip_lo, clip_hi;
+    unsigned int n_events;          // clip events appended (may exceed capacity: then events were dropped)
+    unsigned int pad;
+};
+
+struct ClipEvent { int job; int ch_kind; long long frame; };   // ch_kind = channel | (1<<16 if high clip)
+
+static const int kMaxPhasesDev = 20;
+static const int kMaxFirTapsDev = 176;
+static const int kMaxFir3TapsDev = 32;
+
+struct KParams {
+    const DevJob* jobs;
+    int njobs;
+    unsigned int total_tiles;
+    const double* lut;        // global copy of the stage-1 LUT (copied to shared memory per CTA)
+    int lut_doubles;
+
+    // input format (A1)
+    int C, layout, lsb_first, block_size;
+    // writer (A13-A17)
+    int bits, bps, out_format, dither, has_ds, peak;
+    double scale, neg_scale, pos_scale;
+
+    int TF;                   // output frames per tile
+    int tile_stride;          // shared-memory bytes per channel input tile
+
+    // integer path (A3/A4)
+    int h, nt, bpo;
+    // L/M path (A6-A10)
+    int nstages, L, m1, accum, h1, gmax, ring_mask;
+    long long e0;
+    int h2, D2, h3, D3;
+    int s1_cap, s2_cap;       // doubles reserved for the stage-1 / stage-2 tiles
+    unsigned char groups[kMaxPhasesDev];
+
+    DevStats* stats;
+    ClipEvent* events;
+    unsigned int ev_cap;
+
+    double c2[kMaxFirTapsDev];   // first h2 entries of reverse(half2): the taps convolve_direct walks
+    double c3[kMaxFir3TapsDev];
+};
+
+}  // namespace d2p

@@ -1,0 +1,20 @@
+// d2p_launch.h -- host-visible launch interface of d2p_kernels.cu.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "d2p_device.h"
+
+#define D2P_DEV_OUT_LE 0
+#define D2P_DEV_OUT_BE 1
+#define D2P_DEV_OUT_PLANAR 2
+
+namespace d2p {
+
+static const int kMaxThreads = 512;          // CTA size (launch bound of both kernels)
+static const int kMaxSmem = 227 * 1024;      // opt-in dynamic shared memory per CTA on sm_100a
+
+const char* kernel_name(bool lm);
+int max_ctas_per_sm(bool lm, int threads, size_t smem);   // occupancy of the kernel at this geometry (0 on error)
+cudaError_t launch_kernels(const KParams& P, bool lm, int grid, int threads, size_t smem, cudaStream_t stream);
+
+}  // namespace d2p

@@ -1,0 +1,166 @@
+/*
+ * dsd2pcm_b200.h -- C ABI of libdsd2pcm_b200.so: the rdsd2pcm conversion core (DSD unpack ->
+ * LUT-FIR decimate / L-M resample -> scale / dither / quantise / pack) on NVIDIA B200 (sm_100a).
+ *
+ * This is the drop-in boundary for clone206/dsd2dxd's `rdsd2pcm` library.  The reference has no
+ * FFI of its own; the seam these entry points replace is the body of
+ *     ConversionContext::process_blocks          rd/conversion_context.rs:295-328
+ *         process_channel(chan, &chan_bufs[chan])   :376-398  (BytePrecalcDecimator::process_bytes
+ *                                                   rd/byte_precalc_decimator.rs:112 |
+ *                                                   LMResampler::process_bytes_lm rd/lm_resampler.rs:270)
+ *         PcmWriter::write_to_buffer(n, chan)       rd/pcm_writer.rs:608
+ * plus the constructor parameter set of Rdsd2Pcm::new / from_container (rd/lib.rs:75-91, 171-182).
+ * (rd/ = src/rdsd2pcm/src/ of the reference.)  INTEGRATION.md shows the Rust `extern "C"` block
+ * and the call-site patch.
+ *
+ * Plain C types only.  All functions return a d2p_status (0 = success) unless noted; none aborts.
+ * There is no CPU fallback: without a CUDA device every compute entry returns D2P_ERR_NO_DEVICE.
+ * A d2p_ctx is owned by one thread at a time (like one Rdsd2Pcm per Rayon worker).
+ */
+#ifndef DSD2PCM_B200_H
+#define DSD2PCM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define D2P_ABI_VERSION 1
+
+typedef enum d2p_status {
+    D2P_OK = 0,
+    D2P_ERR_INVALID_ARG = 1,
+    D2P_ERR_TAPS_NOT_FOUND = 2,   /* "Taps not found for decimation ratio ..."  rd/conversion_context.rs:155-163 */
+    D2P_ERR_UNSUPPORTED_LM = 3,   /* "Unsupported L/M combination" / "Unsupported 588: ..."  rd/lm_resampler.rs:115,264 */
+    D2P_ERR_BIT_DEPTH = 4,        /* "Unsupported bit depth"  rd/pcm_writer.rs:195-197 */
+    D2P_ERR_NO_DEVICE = 5,        /* no usable CUDA device: the library has no CPU path */
+    D2P_ERR_CUDA = 6,             /* a CUDA call failed; d2p_last_error() has the detail */
+    D2P_ERR_NOMEM = 7,
+    D2P_ERR_STATE = 8,            /* call sequence error (push after finish, ...) */
+    D2P_ERR_CAPACITY = 9          /* output buffer too small */
+} d2p_status;
+
+/* Values are the reference CLI's own option letters (src/main.rs:171-215). */
+enum { D2P_FILTER_EQUIRIPPLE = 'E', D2P_FILTER_XLD = 'X', D2P_FILTER_DSD2PCM = 'D', D2P_FILTER_CHEBYSHEV = 'C' };
+enum { D2P_DITHER_TPDF = 'T', D2P_DITHER_RECT = 'R', D2P_DITHER_FPD = 'F', D2P_DITHER_NONE = 'X' };
+enum { D2P_LAYOUT_PLANAR = 'P', D2P_LAYOUT_INTERLEAVED = 'I' };
+/* Output sample container */
+enum {
+    D2P_OUT_INTERLEAVED_LE = 0,   /* stdout / WAV payload: pack_int / pack_float  rd/pcm_writer.rs:365-396 */
+    D2P_OUT_INTERLEAVED_BE = 1,   /* AIFF / AIFC payload  rd/audio_file.rs:257-275 */
+    D2P_OUT_PLANAR_32 = 2         /* AudioFile<i32|f32>.samples[channel][frame]  rd/pcm_writer.rs:411-421 (20-bit NOT shifted) */
+};
+
+/* Mirrors the parameters of Rdsd2Pcm::new (rd/lib.rs:75-91) that reach the hot path. */
+typedef struct d2p_config {
+    int32_t  dsd_rate;         /* DsdRate: 1 (DSD64), 2, 4, 8 (DSD512)                               */
+    uint32_t out_rate;         /* output PCM rate in Hz (CLI -r)                                     */
+    int32_t  filter;           /* D2P_FILTER_*  (CLI -t)                                             */
+    int32_t  bits;             /* 16, 20, 24 (integer) or 32 (float)  (CLI -b)                       */
+    int32_t  dither;           /* D2P_DITHER_*  (CLI -d)                                             */
+    int32_t  channels;         /* CLI -c                                                             */
+    double   level_db;         /* CLI -l                                                             */
+    int32_t  in_layout;        /* D2P_LAYOUT_*: planar blocks of block_size per channel, or byte-interleaved (CLI -f) */
+    int32_t  lsb_first;        /* Endianness::LsbFirst (CLI -e L) = 1; MSB-first sources are bit-reversed on load */
+    uint32_t block_size;       /* bytes per channel per block (CLI -s; DSF: 4096).  Also the reader chunk that
+                                  orders the FPD dither stream and the clip counter, as in process_blocks.  */
+    int32_t  out_format;       /* D2P_OUT_*                                                          */
+    uint64_t dither_seed;      /* the reference seeds from the OS (irreproducible); here it is explicit */
+    int32_t  has_dither_scale; /* env DSD2DXD_DITHERSCALE present  (rd/dither.rs:39-49)              */
+    double   dither_scale_db;
+    int32_t  device;           /* CUDA device ordinal                                                */
+    int32_t  keep_f64;         /* also keep the pre-scale f64 decimator output per channel (parity)  */
+} d2p_config;
+
+/* What a configuration resolves to (host-only; needs no GPU).  Mirrors
+ * compute_decim_and_upsample (rd/lm_resampler.rs:911), select_precalc_taps
+ * (rd/byte_precalc_decimator.rs:167), LMResampler::new (rd/lm_resampler.rs:87), set_scaling
+ * (rd/pcm_writer.rs:288) and calc_frames_cap (rd/lib.rs:259). */
+typedef struct d2p_plan_info {
+    int32_t  decim_ratio;      /* M */
+    uint32_t upsample_ratio;   /* L (1 = integer path) */
+    int32_t  num_stages;       /* 1 (LUT FIR), 2 or 3 (L/M) */
+    char     stage_table[3][32];
+    int32_t  stage_half_taps[3];
+    int32_t  stage_decim[3];   /* integer path: decim; L/M: m1, D2, D3 */
+    double   scale_factor;
+    int32_t  peak_level;
+    int32_t  bytes_per_sample;
+    uint64_t frames_cap;       /* calc_frames_cap(block_size, M, L) */
+    uint64_t lut_bytes;        /* shared-memory LUT footprint of stage 1 */
+} d2p_plan_info;
+
+typedef struct d2p_ctx d2p_ctx;
+
+/* ---- library ---------------------------------------------------------------------------------- */
+int         d2p_abi_version(void);
+const char* d2p_strerror(int status);          /* reference-style message for a status */
+const char* d2p_last_error(void);              /* thread-local detail of the last failure */
+int         d2p_device_count(void);            /* 0 when no CUDA device is usable */
+
+/* ---- planning (host only) ---------------------------------------------------------------------- */
+int      d2p_plan(const d2p_config* cfg, d2p_plan_info* info);
+/* Frames per channel the reference emits for `bytes_per_channel` input bytes fed in block_size chunks. */
+uint64_t d2p_frames_for_bytes(const d2p_config* cfg, uint64_t bytes_per_channel);
+/* Half-tap table by reference name ("HTAPS_DSD64_8TO1_EQ", ...): returns length, *data -> static f64. */
+int      d2p_tap_table(const char* name, const double** data);
+int      d2p_tap_table_count(void);
+const char* d2p_tap_table_name(int index);
+
+/* ---- streaming conversion: one context per input file ------------------------------------------- */
+int  d2p_create(const d2p_config* cfg, d2p_ctx** out);
+void d2p_destroy(d2p_ctx* ctx);
+/* Feed container-order DSD payload bytes (any chunking; host memory).  Replaces the per-block
+ * process_channel + write_to_buffer pair: all frames that become computable are produced on the GPU. */
+int  d2p_push(d2p_ctx* ctx, const uint8_t* raw, size_t nbytes);
+/* End of input: a trailing partial block group is split evenly between channels. */
+int  d2p_finish(d2p_ctx* ctx);
+/* Frames produced and not yet pulled. */
+uint64_t d2p_frames_ready(const d2p_ctx* ctx);
+/* Copy up to cap_bytes of packed PCM (out_format layout) to host memory; *frames = frames copied.
+ * For D2P_OUT_PLANAR_32, `pcm` receives channel-major int32/f32 with `*frames` per channel. */
+int  d2p_pull(d2p_ctx* ctx, void* pcm, size_t cap_bytes, uint64_t* frames);
+/* Pre-scale f64 output of one channel (needs keep_f64): frames [first, first+cap) counted from the
+ * oldest frame not yet pulled by d2p_pull.  Does not consume. */
+int  d2p_pull_f64(d2p_ctx* ctx, int chan, double* out, size_t cap, uint64_t* n);
+/* clips: PcmWriter::clips semantics (rd/pcm_writer.rs:658-675); peak_abs: max |sample*scale|
+ * (process_levels, rd/conversion_context.rs:209-256); clipped_samples: plain count. */
+int  d2p_stats(d2p_ctx* ctx, int64_t* clips, double* peak_abs, int64_t* clipped_samples);
+
+/* ---- whole-payload conversion with host buffers (pipelined H2D / kernel / D2H) ------------------- */
+/* out_cap_bytes must hold d2p_frames_for_bytes(...) * channels * bytes_per_sample. */
+int  d2p_convert_host(const d2p_config* cfg, const uint8_t* raw, size_t nbytes,
+                      void* pcm, size_t out_cap_bytes, uint64_t* frames, int64_t* clips, double* peak_abs);
+/* Pinned host memory for the buffers above (plain malloc'ed memory also works, more slowly). */
+void* d2p_host_alloc(size_t nbytes);
+void  d2p_host_free(void* p);
+
+/* ---- device-resident batch: many payloads already in HBM, one launch set ------------------------- */
+typedef struct d2p_job {
+    const void* d_in;          /* device pointer: container-order payload */
+    uint64_t    in_bytes;      /* payload bytes (all channels) */
+    void*       d_out;         /* device pointer: packed PCM, out_format layout */
+    uint64_t    out_cap_bytes;
+    double*     d_f64;         /* optional device pointer: channels * f64_stride doubles (may be NULL) */
+    uint64_t    f64_stride;
+    uint64_t    dither_seed;   /* per-file seed */
+    uint64_t    frames;        /* out: frames per channel written */
+} d2p_job;
+
+typedef struct d2p_batch d2p_batch;
+int  d2p_batch_create(const d2p_config* cfg, d2p_batch** out);
+void d2p_batch_destroy(d2p_batch* b);
+/* Enqueue the conversion of all jobs on `cuda_stream` (a cudaStream_t; NULL = default stream).
+ * Asynchronous: returns after the launches; jobs[i].frames is filled before returning. */
+int  d2p_batch_run(d2p_batch* b, d2p_job* jobs, int njobs, void* cuda_stream);
+/* Number of kernel launches issued by this batch object so far, and the names last launched. */
+uint64_t d2p_batch_launches(const d2p_batch* b);
+/* Sum over jobs of clipped samples / max |sample*scale| since creation (synchronises the stream). */
+int  d2p_batch_stats(d2p_batch* b, void* cuda_stream, int64_t* clipped_samples, double* peak_abs);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DSD2PCM_B200_H */

@@ -1,0 +1,234 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the CPU oracle on the same inputs.
+
+Bit-exact for the pre-scale f64 samples and for integer / f32 PCM with dither off; exact against the
+oracle's Philox dither with dither on, and within +-1 LSB of the undithered output.
+"""
+import hashlib
+
+import numpy as np
+import pytest
+
+import dsd2dxd_b200 as d2p
+from dsd2dxd_b200 import _capi
+from oracle import orclib
+
+pytestmark = pytest.mark.gpu
+
+# every (dsd_rate, out_rate, filter) the reference resolves on the integer path (A2) ...
+INT_COMBOS = [
+    (1, 352800, "D"), (1, 352800, "X"), (1, 352800, "E"), (2, 705600, "E"), (4, 1411200, "E"),
+    (1, 176400, "X"), (1, 176400, "E"), (2, 352800, "E"), (2, 352800, "C"), (2, 352800, "X"), (4, 705600, "E"),
+    (1, 88200, "X"), (1, 88200, "E"), (2, 176400, "E"), (2, 176400, "C"), (4, 352800, "E"), (8, 705600, "E"),
+    (2, 88200, "E"), (2, 88200, "C"), (4, 176400, "E"), (8, 352800, "E"), (1, 44100, "E"),
+    (4, 88200, "E"),
+]
+# ... and every L/M topology (A6), including the unguarded DSD512 rows (F8)
+LM_COMBOS = [(r, o) for r in (1, 2, 4, 8) for o in (96000, 192000, 384000)]
+
+
+def run_gpu(raw, chunks=None, **kw):
+    cfg = d2p.make_config(keep_f64=True, **kw)
+    conv = d2p.Converter(cfg)
+    pcm, f64 = [], [[] for _ in range(cfg.channels)]
+    pieces = [raw] if chunks is None else np.split(raw, chunks)
+    for i, piece in enumerate(pieces):
+        if piece.size:
+            conv.push(piece)
+        if i == len(pieces) - 1:
+            conv.finish()
+        for c in range(cfg.channels):
+            f64[c].append(conv.peek_f64(c))
+        pcm.append(conv.pull())
+    st = conv.stats()
+    conv.close()
+    if cfg.out_format == _capi.OUT_PLANAR_32:
+        pcm = np.concatenate(pcm, axis=1)
+    else:
+        pcm = np.concatenate(pcm)
+    return pcm, np.stack([np.concatenate(x) for x in f64]), st
+
+
+def rand_payload(seed, channels, blocks, block=4096):
+    return np.random.default_rng(seed).integers(0, 256, size=channels * blocks * block, dtype=np.uint8)
+
+
+@pytest.mark.parametrize("dsd_rate,out_rate,filt", INT_COMBOS)
+def test_integer_path_bit_exact(dsd_rate, out_rate, filt):
+    raw = rand_payload(dsd_rate * 1000 + out_rate % 997, 2, 5)
+    ref = orclib.convert(raw, dsd_rate=dsd_rate, out_rate=out_rate, filt=filt, bits=24, channels=2)
+    pcm, f64, _ = run_gpu(raw, dsd_rate=dsd_rate, out_rate=out_rate, filt=filt, bits=24, channels=2)
+    assert f64.shape == ref.f64.shape
+    assert np.array_equal(f64, ref.f64)
+    assert np.array_equal(pcm, ref.pcm)
+
+
+@pytest.mark.parametrize("dsd_rate,out_rate", LM_COMBOS)
+def test_lm_path_bit_exact(dsd_rate, out_rate):
+    raw = rand_payload(dsd_rate * 7 + out_rate % 991, 2, 6)
+    ref = orclib.convert(raw, dsd_rate=dsd_rate, out_rate=out_rate, bits=24, channels=2)
+    pcm, f64, _ = run_gpu(raw, dsd_rate=dsd_rate, out_rate=out_rate, bits=24, channels=2)
+    assert f64.shape == ref.f64.shape
+    assert np.array_equal(f64, ref.f64)
+    assert np.array_equal(pcm, ref.pcm)
+
+
+@pytest.mark.parametrize("bits", [16, 20, 24, 32])
+@pytest.mark.parametrize("out_rate", [352800, 192000])
+@pytest.mark.parametrize("level_db", [0.0, -4.0, 9.0])
+def test_bit_depths_levels_and_clipping(bits, out_rate, level_db):
+    raw = rand_payload(bits + out_rate % 13, 2, 4)
+    # a loud low-frequency square wave on top of noise makes +9 dB clip in runs
+    raw[: raw.size // 2] = np.repeat(np.array([0xFF, 0xFF, 0x00, 0x00] * 8, dtype=np.uint8), raw.size // 64)[: raw.size // 2]
+    ref = orclib.convert(raw, dsd_rate=1, out_rate=out_rate, bits=bits, level_db=level_db, channels=2)
+    pcm, f64, st = run_gpu(raw, dsd_rate=1, out_rate=out_rate, bits=bits, level_db=level_db, channels=2)
+    assert np.array_equal(pcm, ref.pcm)
+    if bits != 32:
+        assert st["clips"] == ref.clips
+    assert st["peak_abs"] == np.abs(ref.f64 * ref.scale).max()
+
+
+@pytest.mark.parametrize("out_format", [_capi.OUT_INTERLEAVED_BE, _capi.OUT_PLANAR_32])
+@pytest.mark.parametrize("bits", [16, 20, 24, 32])
+def test_output_containers(out_format, bits):
+    raw = rand_payload(99 + bits, 2, 3)
+    pcm, _, _ = run_gpu(raw, dsd_rate=1, out_rate=352800, bits=bits, channels=2, out_format=out_format)
+    ref = orclib.convert(raw, dsd_rate=1, out_rate=352800, bits=bits, channels=2, stdout_mode=False)
+    if out_format == _capi.OUT_PLANAR_32:
+        assert np.array_equal(pcm, ref.planar)          # AudioFile samples: 20-bit values NOT shifted
+    else:
+        # AIFF/AIFC payload: big-endian, 20-bit left-aligned in 3 bytes (rd/audio_file.rs:257-275)
+        q = ref.planar.T
+        if bits == 32:
+            exp = np.ascontiguousarray(q, dtype=">f4").view(np.uint8).reshape(-1)
+        elif bits == 16:
+            exp = q.astype(">i2").view(np.uint8).reshape(-1)
+        else:
+            v = (q << 4 if bits == 20 else q).astype(np.uint32)
+            exp = np.stack([(v >> 16) & 0xFF, (v >> 8) & 0xFF, v & 0xFF], axis=-1).astype(np.uint8).reshape(-1)
+        assert np.array_equal(pcm, exp)
+
+
+@pytest.mark.parametrize("channels,layout,lsb_first", [(1, "P", True), (2, "I", False), (6, "I", False), (3, "P", False), (2, "I", True)])
+@pytest.mark.parametrize("out_rate", [352800, 96000])
+def test_input_layouts(channels, layout, lsb_first, out_rate):
+    raw = rand_payload(channels * 31 + out_rate % 7, channels, 4)
+    ref = orclib.convert(raw, dsd_rate=1, out_rate=out_rate, channels=channels, layout=layout, lsb_first=lsb_first)
+    pcm, f64, _ = run_gpu(raw, dsd_rate=1, out_rate=out_rate, channels=channels, layout=layout, lsb_first=lsb_first)
+    assert np.array_equal(f64, ref.f64)
+    assert np.array_equal(pcm, ref.pcm)
+
+
+@pytest.mark.parametrize("out_rate", [352800, 88200, 96000, 384000])
+@pytest.mark.parametrize("layout", ["P", "I"])
+def test_streaming_chunking_equals_one_shot(out_rate, layout):
+    """State persists across pushes (8b): ragged pushes == one push == oracle."""
+    raw = rand_payload(5 + out_rate % 11, 2, 6)
+    ref = orclib.convert(raw, dsd_rate=1, out_rate=out_rate, channels=2, layout=layout)
+    cuts = [1, 17, 4096, 8191, 8192 * 2 + 5, 40000]
+    pcm, f64, _ = run_gpu(raw, chunks=cuts, dsd_rate=1, out_rate=out_rate, channels=2, layout=layout)
+    assert np.array_equal(f64, ref.f64)
+    assert np.array_equal(pcm, ref.pcm)
+
+
+@pytest.mark.parametrize("nbytes", [0, 2, 100, 4096 * 2 - 2, 4096 * 2 * 3 + 2 * 1000])
+@pytest.mark.parametrize("out_rate", [352800, 96000])
+def test_empty_and_ragged_inputs(nbytes, out_rate):
+    raw = rand_payload(3, 2, 4)[:nbytes]
+    ref = orclib.convert(raw, dsd_rate=1, out_rate=out_rate, channels=2)
+    pcm, f64, _ = run_gpu(raw, dsd_rate=1, out_rate=out_rate, channels=2)
+    assert f64.shape[1] == ref.frames[0]
+    assert np.array_equal(pcm, ref.pcm)
+
+
+@pytest.mark.parametrize("dither", ["T", "R"])
+@pytest.mark.parametrize("out_rate", [88200, 192000])
+def test_dither_exact_and_within_one_lsb(dither, out_rate):
+    raw = rand_payload(77, 2, 5)
+    kw = dict(dsd_rate=2, out_rate=out_rate, bits=24, channels=2)
+    clean = orclib.convert(raw, dither="X", stdout_mode=False, **kw).planar
+    ref = orclib.convert(raw, dither=dither, dither_seed=1234, stdout_mode=False, **kw).planar
+    got, _, _ = run_gpu(raw, dither=dither, dither_seed=1234, out_format=_capi.OUT_PLANAR_32, **kw)
+    assert np.array_equal(got, ref)                                  # same counter-based noise definition
+    assert np.abs(got.astype(np.int64) - clean).max() <= 1           # F5: |dithered - undithered| <= 1 LSB
+    other, _, _ = run_gpu(raw, dither=dither, dither_seed=99, out_format=_capi.OUT_PLANAR_32, **kw)
+    assert not np.array_equal(other, got)
+
+
+def test_dither_scale_env_equivalent():
+    raw = rand_payload(78, 2, 3)
+    kw = dict(dsd_rate=1, out_rate=352800, bits=16, channels=2, dither="T", dither_seed=5, dither_scale_db=6.0)
+    ref = orclib.convert(raw, **kw)
+    pcm, _, _ = run_gpu(raw, **kw)
+    assert np.array_equal(pcm, ref.pcm)
+
+
+def test_fixture_excerpts_match_oracle_and_golden_digests(fixtures, golden_digests):
+    for name, (raw, meta) in fixtures.items():
+        for out_rate, bits in ((352800, 24), (176400, 16), (96000, 24), (192000, 32)):
+            kw = dict(dsd_rate=meta["dsd_rate"], out_rate=out_rate, bits=bits, channels=meta["channels"],
+                      layout=meta["layout"], lsb_first=meta["lsb_first"])
+            pcm, f64, _ = run_gpu(raw, **kw)
+            g = golden_digests[f"{name}/{out_rate}/{bits}"]
+            assert f64.shape[1] == g["frames"]
+            assert hashlib.sha256(pcm.tobytes()).hexdigest() == g["pcm_sha256"], (name, out_rate, bits)
+            assert hashlib.sha256(f64.tobytes()).hexdigest() == g["f64_sha256"], (name, out_rate, bits)
+
+
+def test_impulse_known_answer(fixtures):
+    """KAT: one +2 impulse on the idle pattern reproduces 2*h of the tap table; idle gives exactly 0.0."""
+    raw, meta = fixtures["impulse_mono_toggle"]
+    _, f64, _ = run_gpu(raw, dsd_rate=1, out_rate=352800, channels=1)
+    half = d2p.tap_table("HTAPS_DSD64_8TO1_EQ")
+    nz = np.nonzero(f64[0])[0]
+    assert nz.min() == 1995 and nz.max() == 2007
+    full = np.concatenate([half[::-1], half])
+    # byte 2048 bit 0 flips -1 -> +1: frame n sees it at tap index 8*(n+h-1+1) - 8*nt... -> decimated taps
+    got = f64[0][1995:2008]
+    best = min(np.abs(got - 2 * full[o::8][:13]).max() for o in range(8) if full[o::8].size >= 13)
+    assert best < 1e-16
+
+
+def test_convert_host_pipelined_matches_streaming():
+    raw = rand_payload(11, 2, 40)
+    for out_rate in (352800, 192000):
+        cfg = d2p.make_config(dsd_rate=1, out_rate=out_rate, channels=2)
+        pcm, frames, _ = d2p.convert_host(cfg, raw)
+        ref = orclib.convert(raw, dsd_rate=1, out_rate=out_rate, channels=2, want_f64=False)
+        assert frames == ref.frames[0]
+        assert np.array_equal(pcm, ref.pcm)
+
+
+def test_batch_of_device_resident_files_matches_oracle():
+    torch = pytest.importorskip("torch")
+    nfiles = 5
+    raws = [rand_payload(200 + i, 2, 3 + i) for i in range(nfiles)]
+    cfg = d2p.make_config(dsd_rate=4, out_rate=352800, channels=2)
+    batch = d2p.Batch(cfg)
+    d_in = [torch.from_numpy(r).cuda() for r in raws]
+    caps = [d2p.frames_for_bytes(cfg, r.size // 2) * 6 for r in raws]
+    d_out = [torch.zeros(max(c, 16), dtype=torch.uint8, device="cuda") for c in caps]
+    jobs = batch.make_jobs(dict(d_in=i.data_ptr(), in_bytes=i.numel(), d_out=o.data_ptr(), out_cap_bytes=o.numel())
+                           for i, o in zip(d_in, d_out))
+    frames = batch.run(jobs, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert batch.launches() == 1
+    for r, o, f, cap in zip(raws, d_out, frames, caps):
+        ref = orclib.convert(r, dsd_rate=4, out_rate=352800, channels=2, want_f64=False)
+        assert f == ref.frames[0]
+        assert np.array_equal(o.cpu().numpy()[:cap], ref.pcm)
+    batch.close()
+
+
+def test_time_block_split_is_exact():
+    """8e: a long stream cut into halo-padded time blocks gives the same bytes as one pass
+    (size-independent property; 64 MiB-scale input is exercised by bench.py)."""
+    raw = rand_payload(321, 2, 64)
+    cfg = d2p.make_config(dsd_rate=4, out_rate=176400, bits=20, channels=2)
+    whole, frames, _ = d2p.convert_host(cfg, raw)
+    conv = d2p.Converter(cfg)
+    for piece in np.array_split(raw, 13):
+        conv.push(piece)
+    conv.finish()
+    parts = conv.pull()
+    conv.close()
+    assert np.array_equal(whole, parts)
