@@ -217,26 +217,27 @@ struct Launcher {
 // PcmWriter::update_clip_stats (rd/pcm_writer.rs:658-675) replayed over the sparse clip events.
 // Samples are visited in the reference's order: reader block, then channel, then frame.
 struct SeqEvent { unsigned long long seq; int high; };
-static int64_t replay_clips(std::vector<SeqEvent>& ev, int64_t* last_low, int64_t* last_high, unsigned long long* last_seq,
-                            bool* have_last) {
+static int64_t replay_clips(std::vector<SeqEvent>& ev) {
     std::sort(ev.begin(), ev.end(), [](const SeqEvent& a, const SeqEvent& b) { return a.seq < b.seq; });
-    int64_t clips = 0;
+    int64_t clips = 0, last_low = 0, last_high = 0;
+    unsigned long long last_seq = 0;
+    bool have_last = false;
     for (const SeqEvent& e : ev) {
-        if (!*have_last || e.seq != *last_seq + 1) { *last_low = 0; *last_high = 0; }   // an unclipped sample in between
-        if (!e.high) { if (*last_low == 1) ++clips; *last_low += 1; }
-        else { *last_low = 0; if (*last_high == 1) ++clips; *last_high += 1; }
-        *last_seq = e.seq; *have_last = true;
+        if (!have_last || e.seq != last_seq + 1) { last_low = 0; last_high = 0; }   // an unclipped sample in between
+        if (!e.high) { if (last_low == 1) ++clips; last_low += 1; }                  // a low clip leaves last_high alone
+        else { last_low = 0; if (last_high == 1) ++clips; last_high += 1; }
+        last_seq = e.seq; have_last = true;
     }
     return clips;
 }
 
 // Position of (channel, frame) in the reference's processing order for a stream fed in block_size chunks.
-static unsigned long long seq_index(const Plan& p, int ch, long long f) {
+static unsigned long long seq_index(const Plan& p, int ch, long long f, long long total_q) {
     const long long B = p.cfg.block_size;
     const long long need = p.bytes_needed_for_frames(f + 1);       // frame f appears in the block containing byte need-1
     const long long blk = (need - 1) / B;
     const long long f_before = p.frames_for_bytes(blk * B);
-    const long long f_after = p.frames_for_bytes((blk + 1) * B);
+    const long long f_after = p.frames_for_bytes(std::min((blk + 1) * B, total_q));
     return (unsigned long long)(p.cfg.channels * f_before + (long long)ch * (f_after - f_before) + (f - f_before));
 }
 
@@ -268,11 +269,9 @@ struct d2p_ctx {
     long long frames_pulled = 0;
     bool finished = false;
     std::deque<OutChunk> ready;
-    // clip replay state
-    int64_t clips = 0, last_low = 0, last_high = 0;
-    unsigned long long last_seq = 0;
-    bool have_last = false, clips_inexact = false;
-    unsigned int events_seen = 0;
+    // clip events reported by the kernels so far (replayed in d2p_stats)
+    std::vector<ClipEvent> clip_events;
+    bool clips_inexact = false;
 };
 
 static size_t group_bytes(const d2p_config& c) {
@@ -286,17 +285,13 @@ static int ctx_collect_events(d2p_ctx* ctx) {
     const unsigned int n = st.n_events;
     if (n > kEventCap) ctx->clips_inexact = true;
     const unsigned int take = std::min(n, kEventCap);
-    if (take) {
-        std::vector<ClipEvent> ev(take);
-        CK(cudaMemcpy(ev.data(), ctx->launcher.d_events, sizeof(ClipEvent) * take, cudaMemcpyDeviceToHost));
-        std::vector<SeqEvent> se(take);
-        for (unsigned int i = 0; i < take; ++i) {
-            se[i].seq = seq_index(ctx->dp->plan, ev[i].ch_kind & 0xFFFF, ev[i].frame);
-            se[i].high = (ev[i].ch_kind >> 16) & 1;
-        }
-        ctx->clips += replay_clips(se, &ctx->last_low, &ctx->last_high, &ctx->last_seq, &ctx->have_last);
-        CK(cudaMemsetAsync(&ctx->launcher.d_stats->n_events, 0, sizeof(unsigned int), ctx->stream));
+    if (ctx->clip_events.size() + take > (8u << 20)) ctx->clips_inexact = true;     // heavy clipping: give up on the exact count
+    else if (take) {
+        const size_t old = ctx->clip_events.size();
+        ctx->clip_events.resize(old + take);
+        CK(cudaMemcpy(ctx->clip_events.data() + old, ctx->launcher.d_events, sizeof(ClipEvent) * take, cudaMemcpyDeviceToHost));
     }
+    if (n) CK(cudaMemsetAsync(&ctx->launcher.d_stats->n_events, 0, sizeof(unsigned int), ctx->stream));
     return D2P_OK;
 }
 
@@ -572,7 +567,18 @@ int d2p_stats(d2p_ctx* ctx, int64_t* clips, double* peak_abs, int64_t* clipped_s
     DevStats st;
     CK(cudaMemcpyAsync(&st, ctx->launcher.d_stats, sizeof st, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
-    if (clips) *clips = ctx->clips_inexact ? -1 : ctx->clips;
+    if (clips) {
+        if (ctx->clips_inexact) *clips = -1;
+        else {
+            const Plan& p = ctx->dp->plan;
+            std::vector<SeqEvent> se(ctx->clip_events.size());
+            for (size_t i = 0; i < se.size(); ++i) {
+                se[i].seq = seq_index(p, ctx->clip_events[i].ch_kind & 0xFFFF, ctx->clip_events[i].frame, ctx->have_q);
+                se[i].high = (ctx->clip_events[i].ch_kind >> 16) & 1;
+            }
+            *clips = replay_clips(se);
+        }
+    }
     if (peak_abs) { double d; std::memcpy(&d, &st.peak_bits, 8); *peak_abs = d; }
     if (clipped_samples) *clipped_samples = (int64_t)(st.clip_lo + st.clip_hi);
     return D2P_OK;

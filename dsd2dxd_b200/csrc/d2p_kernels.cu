@@ -440,8 +440,9 @@ static cudaError_t ensure_smem_attr(bool lm) {
     if (e != cudaSuccess) return e;
     const void* fn = lm ? (const void*)lm_kernel : (const void*)lutfir_kernel;
     if (dev < 64 && !attr_done[lm ? 1 : 0][dev]) {
-        e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
-        if (e != cudaSuccess) return e;
+        // the opt-in limit (227 KiB) covers static + dynamic shared memory: leave room for the kernels' statics
+        e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem - 1024);
+        if (e != cudaSuccess) { cudaGetLastError(); return e; }
         attr_done[lm ? 1 : 0][dev] = true;
     }
     return cudaSuccess;
@@ -451,7 +452,7 @@ int max_ctas_per_sm(bool lm, int threads, size_t smem) {
     if (ensure_smem_attr(lm) != cudaSuccess) return 0;
     int n = 0;
     const void* fn = lm ? (const void*)lm_kernel : (const void*)lutfir_kernel;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, threads, smem) != cudaSuccess) return 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, threads, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
     return n;
 }
 

@@ -179,8 +179,10 @@ int make_plan(const d2p_config& cfg, Plan* out, std::string* msg) {
         const TapTable* t = select_precalc(cfg.filter, cfg.dsd_rate, p.M);
         if (!t || p.M % 8 != 0) {
             char buf[200];
-            std::snprintf(buf, sizeof buf, "Taps not found for decimation ratio %d / filter '%c' (dsd_rate %d). ",
-                          p.M, (char)cfg.filter, cfg.dsd_rate);
+            const char* fname = cfg.filter == 'E' ? "Equiripple" : cfg.filter == 'X' ? "XLD" : cfg.filter == 'D' ? "Dsd2Pcm"
+                              : cfg.filter == 'C' ? "Chebyshev" : "?";                 // FilterType's Debug names
+            std::snprintf(buf, sizeof buf, "Taps not found for decimation ratio %d / filter '%s' (dsd_rate %d). ",
+                          p.M, fname, cfg.dsd_rate);
             return fail(D2P_ERR_TAPS_NOT_FOUND, buf);
         }
         p.tab[0] = t; p.sdecim[0] = p.M; p.nstages = 1;

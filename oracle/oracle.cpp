@@ -862,8 +862,10 @@ int orc_convert(const orc_config* cfg, const uint8_t* raw, size_t nbytes,
         const char* tn = select_precalc_taps_name(cfg->filter, cfg->dsd_rate, decim_ratio);
         if (!tn) {
             char buf[160];
-            std::snprintf(buf, sizeof buf, "Taps not found for decimation ratio %d / filter '%c' (dsd_rate %d). ",
-                          decim_ratio, cfg->filter, cfg->dsd_rate);
+            const char* fname = cfg->filter == 'E' ? "Equiripple" : cfg->filter == 'X' ? "XLD"
+                              : cfg->filter == 'D' ? "Dsd2Pcm" : cfg->filter == 'C' ? "Chebyshev" : "?";
+            std::snprintf(buf, sizeof buf, "Taps not found for decimation ratio %d / filter '%s' (dsd_rate %d). ",
+                          decim_ratio, fname, cfg->dsd_rate);
             return fail(err, errcap, buf);
         }
         const TapTable& t = kTables[table_id(tn)];

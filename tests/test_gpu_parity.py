@@ -97,7 +97,7 @@ def test_output_containers(out_format, bits):
         assert np.array_equal(pcm, ref.planar)          # AudioFile samples: 20-bit values NOT shifted
     else:
         # AIFF/AIFC payload: big-endian, 20-bit left-aligned in 3 bytes (rd/audio_file.rs:257-275)
-        q = ref.planar.T
+        q = np.ascontiguousarray(ref.planar.T)
         if bits == 32:
             exp = np.ascontiguousarray(q, dtype=">f4").view(np.uint8).reshape(-1)
         elif bits == 16:
