@@ -182,6 +182,13 @@ class Batch:
         _capi.check(_capi.lib().d2p_batch_run(self._h, jobs, len(jobs), C.c_void_p(stream)))
         return [int(j.frames) for j in jobs]
 
+    def convert_host(self, raw, out):
+        """raw/out: uint8 numpy views of host memory (ideally HostBuffer.array).  Returns frames."""
+        frames = C.c_uint64()
+        _capi.check(_capi.lib().d2p_batch_convert_host(self._h, raw.ctypes.data, raw.size, out.ctypes.data, out.size,
+                                                       C.byref(frames)))
+        return int(frames.value)
+
     def launches(self):
         return int(_capi.lib().d2p_batch_launches(self._h))
 

@@ -49,7 +49,8 @@ EXPORTS = [
     "d2p_plan", "d2p_frames_for_bytes", "d2p_tap_table", "d2p_tap_table_count", "d2p_tap_table_name",
     "d2p_create", "d2p_destroy", "d2p_push", "d2p_finish", "d2p_frames_ready", "d2p_pull", "d2p_pull_f64", "d2p_stats",
     "d2p_convert_host", "d2p_host_alloc", "d2p_host_free",
-    "d2p_batch_create", "d2p_batch_destroy", "d2p_batch_run", "d2p_batch_launches", "d2p_batch_stats",
+    "d2p_batch_create", "d2p_batch_destroy", "d2p_batch_run", "d2p_batch_convert_host", "d2p_batch_launches",
+    "d2p_batch_stats",
 ]
 
 _lib = None
@@ -95,6 +96,7 @@ def lib():
     L.d2p_batch_destroy.argtypes = [vp]
     L.d2p_batch_destroy.restype = None
     L.d2p_batch_run.argtypes = [vp, C.POINTER(Job), C.c_int, vp]
+    L.d2p_batch_convert_host.argtypes = [vp, vp, C.c_size_t, vp, C.c_size_t, C.POINTER(C.c_uint64)]
     L.d2p_batch_launches.restype = C.c_uint64
     L.d2p_batch_launches.argtypes = [vp]
     L.d2p_batch_stats.argtypes = [vp, vp, C.POINTER(C.c_int64), C.POINTER(C.c_double)]

@@ -593,15 +593,49 @@ void* d2p_host_alloc(size_t nbytes) {
 void d2p_host_free(void* p) { if (p) cudaFreeHost(p); }
 
 // ---- whole payload, host buffers, pipelined ---------------------------------------------------------
-int d2p_convert_host(const d2p_config* cfg, const uint8_t* raw, size_t nbytes, void* pcm, size_t out_cap_bytes,
-                     uint64_t* frames, int64_t* clips, double* peak_abs) {
-    if (!cfg || (!raw && nbytes) || !pcm || !frames) return set_err(D2P_ERR_INVALID_ARG, "null argument");
-    if (cfg->out_format == D2P_OUT_PLANAR_32 || cfg->keep_f64)
-        return set_err(D2P_ERR_INVALID_ARG, "d2p_convert_host produces interleaved packed PCM only");
-    DevicePlan* dp = nullptr;
-    int st = build_device_plan(*cfg, &dp);
-    if (st != D2P_OK) return st;
-    const Plan& p = dp->plan;
+// HostPipe: three streams, each with its own device input/output staging, reused across calls.
+// Chunk i runs H2D -> kernel -> D2H on stream i%3, so the copies of neighbouring chunks overlap the
+// kernel (PCIe is full duplex).  Every chunk ships its own filter halo, so chunks are independent.
+namespace d2p {
+struct HostPipe {
+    static const int NS = 3;
+    cudaStream_t streams[NS] = {nullptr, nullptr, nullptr};
+    uint8_t* d_in[NS] = {nullptr, nullptr, nullptr};
+    uint8_t* d_out[NS] = {nullptr, nullptr, nullptr};
+    size_t in_cap = 0, out_cap = 0;
+    bool ready = false;
+
+    int init() {
+        if (ready) return D2P_OK;
+        for (int s = 0; s < NS; ++s) CK(cudaStreamCreateWithFlags(&streams[s], cudaStreamNonBlocking));
+        ready = true;
+        return D2P_OK;
+    }
+    int reserve(size_t in_need, size_t out_need) {
+        if (in_need > in_cap) {
+            for (int s = 0; s < NS; ++s) { if (d_in[s]) cudaFree(d_in[s]); d_in[s] = nullptr; }
+            for (int s = 0; s < NS; ++s) if (cudaMalloc(&d_in[s], in_need) != cudaSuccess) { cudaGetLastError(); in_cap = 0; return set_err(D2P_ERR_NOMEM, "device allocation failed"); }
+            in_cap = in_need;
+        }
+        if (out_need > out_cap) {
+            for (int s = 0; s < NS; ++s) { if (d_out[s]) cudaFree(d_out[s]); d_out[s] = nullptr; }
+            for (int s = 0; s < NS; ++s) if (cudaMalloc(&d_out[s], out_need) != cudaSuccess) { cudaGetLastError(); out_cap = 0; return set_err(D2P_ERR_NOMEM, "device allocation failed"); }
+            out_cap = out_need;
+        }
+        return D2P_OK;
+    }
+    void destroy() {
+        for (int s = 0; s < NS; ++s) {
+            if (streams[s]) { cudaStreamSynchronize(streams[s]); cudaStreamDestroy(streams[s]); }
+            if (d_in[s]) cudaFree(d_in[s]);
+            if (d_out[s]) cudaFree(d_out[s]);
+        }
+    }
+};
+
+static int host_convert(const DevicePlan& dp, Launcher& launcher, HostPipe& pipe, const uint8_t* raw, size_t nbytes,
+                        void* pcm, size_t out_cap_bytes, uint64_t* frames, size_t chunk_bytes) {
+    const Plan& p = dp.plan;
     const d2p_config& c = p.cfg;
     const bool planar = c.in_layout == D2P_LAYOUT_PLANAR;
     const size_t G = group_bytes(c);
@@ -612,36 +646,17 @@ int d2p_convert_host(const d2p_config* cfg, const uint8_t* raw, size_t nbytes, v
     const long long total_frames = p.frames_for_bytes(total_q);
     const size_t fb = (size_t)c.channels * p.bps;
     *frames = 0;
-    if ((size_t)total_frames * fb > out_cap_bytes) { free_device_plan(dp); return set_err(D2P_ERR_CAPACITY, "output buffer too small"); }
+    if ((size_t)total_frames * fb > out_cap_bytes) return set_err(D2P_ERR_CAPACITY, "output buffer too small");
+    int rc = pipe.init();
+    if (rc != D2P_OK) return rc;
 
-    const int NS = 3;
-    const long long chunk_groups = std::max<long long>(1, (long long)((64u << 20) / G));   // ~64 MiB of payload per chunk
-    cudaStream_t streams[NS]; uint8_t* d_in[NS] = {nullptr, nullptr, nullptr}; uint8_t* d_out[NS] = {nullptr, nullptr, nullptr};
-    size_t in_cap = 0, out_cap = 0;
-    Launcher launcher;
-    int rc = D2P_OK;
-    auto cleanup = [&]() {
-        for (int s = 0; s < NS; ++s) { if (streams[s]) { cudaStreamSynchronize(streams[s]); cudaStreamDestroy(streams[s]); }
-                                       if (d_in[s]) cudaFree(d_in[s]); if (d_out[s]) cudaFree(d_out[s]); }
-        launcher.destroy();
-        free_device_plan(dp);
-    };
-    for (int s = 0; s < NS; ++s) streams[s] = nullptr;
-    for (int s = 0; s < NS; ++s) if (cudaStreamCreateWithFlags(&streams[s], cudaStreamNonBlocking) != cudaSuccess) { cleanup(); return set_err(D2P_ERR_CUDA, "stream create"); }
-    if ((rc = launcher.init(false)) != D2P_OK) { cleanup(); return rc; }
-
-    // worst-case chunk footprint: chunk + halo groups (+ ragged tail on the last one)
-    const long long max_halo_q = 4096 + 2LL * p.nt + 64;                  // bytes per channel; generous for every topology
-    const long long halo_groups_max = (max_halo_q + unit - 1) / unit + 1;
-    in_cap = (size_t)(chunk_groups + halo_groups_max) * G + (size_t)tail_per * c.channels + 256;
-    {
-        const long long per_chunk_q = chunk_groups * unit + tail_per;
-        const long long fmax = p.frames_for_bytes(per_chunk_q + max_halo_q) + 64;
-        out_cap = (size_t)fmax * fb + 256;
-    }
-    for (int s = 0; s < NS; ++s) {
-        if (cudaMalloc(&d_in[s], in_cap) != cudaSuccess || cudaMalloc(&d_out[s], out_cap) != cudaSuccess) { cleanup(); return set_err(D2P_ERR_NOMEM, "device allocation failed"); }
-    }
+    const long long chunk_groups = std::max<long long>(1, (long long)(chunk_bytes / G));
+    // halo of one chunk: what the first frame of the chunk reads before the chunk's first byte
+    const long long halo_q = p.bytes_needed_for_frames(1) + 64;            // >= filter span in input bytes
+    const long long halo_groups = (halo_q + unit - 1) / unit + (planar ? 1 : 16);
+    const size_t in_need = (size_t)(chunk_groups + halo_groups) * G + (size_t)tail_per * c.channels + 256;
+    const size_t out_need = (size_t)(p.frames_for_bytes((chunk_groups + halo_groups) * unit + tail_per) + 64) * fb + 256;
+    if ((rc = pipe.reserve(in_need, out_need)) != D2P_OK) return rc;
 
     long long f_done = 0;
     int ci = 0;
@@ -651,46 +666,44 @@ int d2p_convert_host(const d2p_config* cfg, const uint8_t* raw, size_t nbytes, v
         const long long end_q = g1 * unit + (last ? tail_per : 0);
         const long long f_new = p.frames_for_bytes(end_q);
         if (f_new > f_done) {
-            const int s = ci % NS; ++ci;
-            long long keep_q = p.first_byte_needed(f_done);
-            long long gk = keep_q / unit;                                  // first group to ship
-            if (!planar) gk = (gk / 16) * 16;                              // keep interleaved chunks 16-aligned per channel
+            const int s = ci % HostPipe::NS; ++ci;
+            long long gk = p.first_byte_needed(f_done) / unit;             // first group to ship (halo included)
+            if (!planar) gk = (gk / 16) * 16;
             const size_t off = (size_t)gk * G;
             const size_t len = (size_t)(g1 - gk) * G + (last ? (size_t)tail_per * c.channels : 0);
-            if (len > in_cap) { rc = set_err(D2P_ERR_NOMEM, "internal: chunk larger than staging buffer"); break; }
-            if (cudaMemcpyAsync(d_in[s], raw + off, len, cudaMemcpyHostToDevice, streams[s]) != cudaSuccess) { rc = cuda_err(cudaGetLastError(), "H2D"); break; }
+            if (len > pipe.in_cap) { rc = set_err(D2P_ERR_NOMEM, "internal: chunk larger than staging buffer"); break; }
+            cudaError_t e = cudaMemcpyAsync(pipe.d_in[s], raw + off, len, cudaMemcpyHostToDevice, pipe.streams[s]);
+            if (e != cudaSuccess) { rc = cuda_err(e, "H2D"); break; }
             std::vector<DevJob> jobs(1);
             DevJob& j = jobs[0];
             std::memset(&j, 0, sizeof j);
-            j.in = d_in[s]; j.base_q = gk * unit; j.end_q = end_q;
+            j.in = pipe.d_in[s]; j.base_q = gk * unit; j.end_q = end_q;
             j.tail_q = (last && tail_per > 0 && planar) ? groups * unit : LLONG_MAX; j.tail_len = tail_per;
             j.f_begin = f_done; j.f_count = f_new - f_done;
-            j.out = d_out[s]; j.seed = c.dither_seed;
-            if ((size_t)j.f_count * fb > out_cap) { rc = set_err(D2P_ERR_NOMEM, "internal: chunk output larger than staging buffer"); break; }
-            if ((rc = launcher.run(*dp, jobs, streams[s])) != D2P_OK) break;
-            if (cudaMemcpyAsync((uint8_t*)pcm + (size_t)f_done * fb, d_out[s], (size_t)j.f_count * fb, cudaMemcpyDeviceToHost, streams[s]) != cudaSuccess) { rc = cuda_err(cudaGetLastError(), "D2H"); break; }
+            j.out = pipe.d_out[s]; j.seed = c.dither_seed;
+            if ((size_t)j.f_count * fb > pipe.out_cap) { rc = set_err(D2P_ERR_NOMEM, "internal: chunk output larger than staging buffer"); break; }
+            if ((rc = launcher.run(dp, jobs, pipe.streams[s])) != D2P_OK) break;
+            e = cudaMemcpyAsync((uint8_t*)pcm + (size_t)f_done * fb, pipe.d_out[s], (size_t)j.f_count * fb, cudaMemcpyDeviceToHost, pipe.streams[s]);
+            if (e != cudaSuccess) { rc = cuda_err(e, "D2H"); break; }
             f_done = f_new;
         }
         if (last) break;
         g0 = g1;
     }
-    for (int s = 0; s < NS; ++s) if (streams[s]) { cudaError_t e = cudaStreamSynchronize(streams[s]); if (e != cudaSuccess && rc == D2P_OK) rc = cuda_err(e, "stream sync"); }
-    if (rc == D2P_OK) {
-        DevStats stt;
-        if (cudaMemcpy(&stt, launcher.d_stats, sizeof stt, cudaMemcpyDeviceToHost) == cudaSuccess) {
-            if (clips) *clips = (int64_t)(stt.clip_lo + stt.clip_hi);      // plain count here; exact replay is the streaming ctx's job
-            if (peak_abs) { double d; std::memcpy(&d, &stt.peak_bits, 8); *peak_abs = d; }
-        }
-        *frames = (uint64_t)f_done;
+    for (int s = 0; s < HostPipe::NS; ++s) {
+        cudaError_t e = cudaStreamSynchronize(pipe.streams[s]);
+        if (e != cudaSuccess && rc == D2P_OK) rc = cuda_err(e, "stream sync");
     }
-    cleanup();
+    if (rc == D2P_OK) *frames = (uint64_t)f_done;
     return rc;
 }
+}  // namespace d2p
 
 // ---- device-resident batch --------------------------------------------------------------------------
 struct d2p_batch {
     DevicePlan* dp = nullptr;
     Launcher launcher;
+    HostPipe pipe;
 };
 
 int d2p_batch_create(const d2p_config* cfg, d2p_batch** out) {
@@ -711,9 +724,32 @@ void d2p_batch_destroy(d2p_batch* b) {
     if (!b) return;
     if (b->dp) cudaSetDevice(b->dp->plan.cfg.device);
     cudaDeviceSynchronize();
+    b->pipe.destroy();
     b->launcher.destroy();
     free_device_plan(b->dp);
     delete b;
+}
+
+int d2p_batch_convert_host(d2p_batch* b, const uint8_t* raw, size_t nbytes, void* pcm, size_t out_cap_bytes,
+                           uint64_t* frames) {
+    if (!b || (!raw && nbytes) || !pcm || !frames) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    const d2p_config& c = b->dp->plan.cfg;
+    if (c.out_format == D2P_OUT_PLANAR_32 || c.keep_f64)
+        return set_err(D2P_ERR_INVALID_ARG, "host conversion produces interleaved packed PCM only");
+    CK(cudaSetDevice(c.device));
+    return host_convert(*b->dp, b->launcher, b->pipe, raw, nbytes, pcm, out_cap_bytes, frames, (size_t)64 << 20);
+}
+
+int d2p_convert_host(const d2p_config* cfg, const uint8_t* raw, size_t nbytes, void* pcm, size_t out_cap_bytes,
+                     uint64_t* frames, int64_t* clips, double* peak_abs) {
+    if (!cfg || !frames) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    d2p_batch* b = nullptr;
+    int st = d2p_batch_create(cfg, &b);
+    if (st != D2P_OK) return st;
+    st = d2p_batch_convert_host(b, raw, nbytes, pcm, out_cap_bytes, frames);
+    if (st == D2P_OK && (clips || peak_abs)) st = d2p_batch_stats(b, nullptr, clips, peak_abs);
+    d2p_batch_destroy(b);
+    return st;
 }
 
 int d2p_batch_run(d2p_batch* b, d2p_job* jobs, int njobs, void* cuda_stream) {

@@ -130,7 +130,8 @@ int  d2p_pull_f64(d2p_ctx* ctx, int chan, double* out, size_t cap, uint64_t* n);
 int  d2p_stats(d2p_ctx* ctx, int64_t* clips, double* peak_abs, int64_t* clipped_samples);
 
 /* ---- whole-payload conversion with host buffers (pipelined H2D / kernel / D2H) ------------------- */
-/* out_cap_bytes must hold d2p_frames_for_bytes(...) * channels * bytes_per_sample. */
+/* out_cap_bytes must hold d2p_frames_for_bytes(...) * channels * bytes_per_sample.
+ * clips receives the plain count of clipped samples (the run-length statistic needs the streaming context). */
 int  d2p_convert_host(const d2p_config* cfg, const uint8_t* raw, size_t nbytes,
                       void* pcm, size_t out_cap_bytes, uint64_t* frames, int64_t* clips, double* peak_abs);
 /* Pinned host memory for the buffers above (plain malloc'ed memory also works, more slowly). */
@@ -155,7 +156,12 @@ void d2p_batch_destroy(d2p_batch* b);
 /* Enqueue the conversion of all jobs on `cuda_stream` (a cudaStream_t; NULL = default stream).
  * Asynchronous: returns after the launches; jobs[i].frames is filled before returning. */
 int  d2p_batch_run(d2p_batch* b, d2p_job* jobs, int njobs, void* cuda_stream);
-/* Number of kernel launches issued by this batch object so far, and the names last launched. */
+/* Whole payload in host memory -> packed interleaved PCM in host memory through this batch object's
+ * persistent pipeline (3 streams; H2D / kernel / D2H of neighbouring 64 MiB chunks overlap).
+ * d2p_convert_host() is this call on a temporary batch object. */
+int  d2p_batch_convert_host(d2p_batch* b, const uint8_t* raw, size_t nbytes, void* pcm, size_t out_cap_bytes,
+                            uint64_t* frames);
+/* Number of kernel launches issued by this batch object so far. */
 uint64_t d2p_batch_launches(const d2p_batch* b);
 /* Sum over jobs of clipped samples / max |sample*scale| since creation (synchronises the stream). */
 int  d2p_batch_stats(d2p_batch* b, void* cuda_stream, int64_t* clipped_samples, double* peak_abs);
