@@ -54,11 +54,33 @@ struct DevicePlan {
 
 static size_t round16(size_t x) { return (x + 15) & ~(size_t)15; }
 
-static void lutfir_geometry(const Plan& p, int TF, int* tile_stride, size_t* smem) {
+// Bank-aware LUT layout of the integer path (see d2p_kernels.cu): R = 16/K replicas of the nt tables in
+// one row per byte value; replica r starts at slot st[r] with st[r] = 0 (mod K) and st[r]/K distinct
+// modulo R, so that lanes (r, c) at table u - c always fall into 16 different 8-byte bank pairs.
+struct LutLayout { int K = 16, R = 1, slots = 0; int st[16] = {0}; };
+
+static LutLayout make_lut_layout(int nt, int K) {
+    LutLayout L;
+    L.K = K; L.R = 16 / K;
+    bool used[16] = {false};
+    int next = 0;
+    for (int r = 0; r < L.R; ++r) {
+        int s = (next + K - 1) / K * K;
+        while (used[(s / K) % L.R]) s += K;
+        used[(s / K) % L.R] = true;
+        L.st[r] = s;
+        next = s + nt;
+    }
+    L.slots = (next + 15) / 16 * 16;
+    return L;
+}
+
+static void lutfir_geometry(const Plan& p, const LutLayout& L, int TF, int* tile_stride, int* in_buf, int* ostage, size_t* smem) {
     const int C = p.cfg.channels;
-    *tile_stride = (int)round16((size_t)TF * p.bpo + 2 * p.nt + 16) + 32;
-    const size_t ostage = p.cfg.out_format == D2P_OUT_PLANAR_32 ? 0 : round16((size_t)TF * C * p.bps);
-    *smem = (size_t)p.nt * 2048 + (size_t)C * *tile_stride + ostage;
+    *tile_stride = (int)round16((size_t)TF * p.bpo + 2 * p.nt + 80) + 16;
+    *in_buf = C * *tile_stride;
+    *ostage = p.cfg.out_format == D2P_OUT_PLANAR_32 ? 0 : (int)round16((size_t)TF * C * p.bps);
+    *smem = (size_t)2 * kLutPad + (size_t)L.slots * 2048 + 2 * (size_t)*in_buf + 2 * (size_t)*ostage;
 }
 
 static void lm_geometry(const Plan& p, int TF, int* tile_stride, int* s1_cap, int* s2_cap, size_t* smem) {
@@ -94,13 +116,9 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
 
     std::vector<double> lut;
     if (dp->lm) build_stage1_lut(p, &lut); else build_bpd_lut(p, &lut);
-    CK(cudaMalloc(&dp->d_lut, lut.size() * sizeof(double)));
-    CK(cudaMemcpy(dp->d_lut, lut.data(), lut.size() * sizeof(double), cudaMemcpyHostToDevice));
 
     KParams& k = dp->kp;
     std::memset(&k, 0, sizeof k);
-    k.lut = dp->d_lut;
-    k.lut_doubles = (int)lut.size();
     k.C = cfg.channels; k.layout = cfg.in_layout; k.lsb_first = cfg.lsb_first ? 1 : 0; k.block_size = (int)cfg.block_size;
     k.bits = cfg.bits; k.bps = p.bps; k.out_format = cfg.out_format; k.dither = cfg.dither;
     k.has_ds = cfg.has_dither_scale ? 1 : 0; k.peak = p.peak;
@@ -120,21 +138,67 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
         }
     }
 
-    // tile geometry: the largest tile that leaves room for two CTAs per SM if the LUT allows, else one
     const size_t budget = (size_t)kMaxSmem - 1024;
-    int best_tf = 0;
-    for (int pass = 0; pass < 2 && !best_tf; ++pass) {
-        const size_t lim = pass == 0 ? budget / 2 : budget;
-        for (int tf = dp->lm ? 512 : 1024; tf >= 64; tf >>= 1) {
-            int ts, a = 0, b = 0; size_t sm;
-            if (dp->lm) lm_geometry(p, tf, &ts, &a, &b, &sm); else lutfir_geometry(p, tf, &ts, &sm);
-            if (sm <= lim && (pass == 1 || tf >= (dp->lm ? 128 : 512))) { best_tf = tf; break; }
+    if (dp->lm) {
+        // tile geometry: the largest tile that leaves room for two CTAs per SM if the LUT allows, else one
+        int best_tf = 0;
+        for (int pass = 0; pass < 2 && !best_tf; ++pass) {
+            const size_t lim = pass == 0 ? budget / 2 : budget;
+            for (int tf = 512; tf >= 64; tf >>= 1) {
+                int ts, a = 0, b = 0; size_t sm;
+                lm_geometry(p, tf, &ts, &a, &b, &sm);
+                if (sm <= lim && (pass == 1 || tf >= 128)) { best_tf = tf; break; }
+            }
         }
+        if (!best_tf) return set_err(D2P_ERR_NOMEM, "filter LUT and tiles do not fit in shared memory");
+        k.TF = best_tf;
+        lm_geometry(p, best_tf, &k.tile_stride, &k.s1_cap, &k.s2_cap, &dp->smem);
+        CK(cudaMalloc(&dp->d_lut, lut.size() * sizeof(double)));
+        CK(cudaMemcpy(dp->d_lut, lut.data(), lut.size() * sizeof(double), cudaMemcpyHostToDevice));
+        k.lut = dp->d_lut;
+        k.lut_doubles = (int)lut.size();
+    } else {
+        // integer path: pick the replication (skew depth K) and the tile size together.  More replicas mean
+        // fewer idle skew steps per frame (nt / (nt + K - 1)) but a larger LUT; one persistent CTA per SM.
+        double best_score = 0.0; LutLayout bestL; int best_tf = 0;
+        for (int K = 1; K <= 16; K <<= 1) {
+            if (K > 1 && K - 1 > p.nt) continue;
+            const LutLayout L = make_lut_layout(p.nt, K);
+            for (int tf = 2048; tf >= 64; tf >>= 1) {
+                int ts, ib, os; size_t sm;
+                lutfir_geometry(p, L, tf, &ts, &ib, &os, &sm);
+                if (sm > budget) continue;
+                const double steps = 4.0 * ((p.nt + K - 1 + 3) / 4);
+                const double ipt = (double)tf * cfg.channels / kMaxThreads;     // frames per consumer thread per tile
+                const double score = (p.nt / steps) * (ipt / (ipt + 0.35));
+                if (score > best_score) { best_score = score; bestL = L; best_tf = tf; }
+                break;
+            }
+        }
+        if (!best_tf) return set_err(D2P_ERR_NOMEM, "filter LUT and tiles do not fit in shared memory");
+        const LutLayout& L = bestL;
+        k.TF = best_tf;
+        k.tf_shift = 0; while ((1 << k.tf_shift) < best_tf) ++k.tf_shift;
+        lutfir_geometry(p, L, best_tf, &k.tile_stride, &k.in_buf_bytes, &k.ostage_bytes, &dp->smem);
+        k.lutK = L.K; k.lut_row_bytes = L.slots * 8;
+        for (int r = 0; r < 16; ++r) k.lut_st[r] = r < L.R ? L.st[r] : 0;
+        k.ngroups = (p.nt + L.K - 1 + 3) / 4;
+        k.gp_lo = (L.K - 1 + 3) / 4;
+        k.gp_hi = p.nt / 4;
+        if (k.gp_hi < k.gp_lo) k.gp_hi = k.gp_lo;
+        if (k.gp_hi > k.ngroups) k.gp_hi = k.ngroups;
+        k.nc = kMaxThreads;
+        dp->threads = kLutfirThreads;
+        std::vector<double> sk((size_t)256 * L.slots, 0.0);
+        for (int b = 0; b < 256; ++b)
+            for (int r = 0; r < L.R; ++r)
+                for (int i = 0; i < p.nt; ++i)
+                    sk[(size_t)b * L.slots + L.st[r] + i] = lut[(size_t)i * 256 + b];
+        CK(cudaMalloc(&dp->d_lut, sk.size() * sizeof(double)));
+        CK(cudaMemcpy(dp->d_lut, sk.data(), sk.size() * sizeof(double), cudaMemcpyHostToDevice));
+        k.lut = dp->d_lut;
+        k.lut_doubles = (int)sk.size();
     }
-    if (!best_tf) return set_err(D2P_ERR_NOMEM, "filter LUT and tiles do not fit in shared memory");
-    k.TF = best_tf;
-    if (dp->lm) lm_geometry(p, best_tf, &k.tile_stride, &k.s1_cap, &k.s2_cap, &dp->smem);
-    else lutfir_geometry(p, best_tf, &k.tile_stride, &dp->smem);
     dp->ctas_per_sm = max_ctas_per_sm(dp->lm, dp->threads, dp->smem);
     if (dp->ctas_per_sm < 1) return set_err(D2P_ERR_CUDA, "kernel cannot be resident with the chosen tile geometry");
     *out = dp.release();

@@ -54,6 +54,16 @@ struct KParams {
 
     // integer path (A3/A4)
     int h, nt, bpo;
+    // skewed, bank-conflict-free LUT layout of the integer path (DESIGN.md "LUT layout"):
+    //   entry (replica r, table i, byte b) lives at  b * lut_row_bytes + (lut_st[r] + i) * 8
+    // lanes of a half-warp are split into R = 16/lutK replicas x lutK skews; lane (r, c) runs table i at
+    // step u = i + c, so the 16 lanes of a half-warp always address 16 distinct 8-byte bank pairs.
+    int lutK, lut_row_bytes;
+    int lut_st[16];
+    int ngroups, gp_lo, gp_hi;   // 4-step groups per frame; [gp_lo, gp_hi) need no activity guard
+    int tf_shift;                // TF == 1 << tf_shift on the integer path
+    int nc;                      // consumer threads (the remaining threads of the CTA stage tiles)
+    int in_buf_bytes, ostage_bytes;   // per buffer (both are double-buffered)
     // L/M path (A6-A10)
     int nstages, L, m1, accum, h1, gmax, ring_mask;
     long long e0;

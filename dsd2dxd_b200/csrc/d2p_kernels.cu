@@ -77,12 +77,13 @@ __device__ __forceinline__ long long planar_offset(const KParams& P, const DevJo
 // into shared memory straight from the container layout (de-interleave / de-block / bit-reverse fused
 // into the load).  Positions outside [0, end_q) read as 0.  s_lo and nbytes are multiples of 16.
 // ------------------------------------------------------------------------------------------------
-__device__ void stage_input(const KParams& P, const DevJob& J, unsigned char* tiles, long long s_lo, int nbytes) {
+__device__ void stage_input(const KParams& P, const DevJob& J, unsigned char* tiles, long long s_lo, int nbytes,
+                            int tid, int nthr) {
     const int C = P.C;
     if (P.layout == 'P') {
         const int nvec = nbytes >> 4;
         const bool fast = ((P.block_size & 15) == 0) && ((((uintptr_t)J.in) & 15) == 0) && ((J.base_q & 15) == 0);
-        for (int v = threadIdx.x; v < nvec * C; v += blockDim.x) {
+        for (int v = tid; v < nvec * C; v += nthr) {
             const int c = v / nvec, idx = v - c * nvec;
             const long long q = s_lo + 16LL * idx;
             uint4 val = make_uint4(0, 0, 0, 0);
@@ -107,7 +108,7 @@ __device__ void stage_input(const KParams& P, const DevJob& J, unsigned char* ti
         // byte-interleaved: consecutive threads read consecutive global bytes (coalesced), scatter to C tiles
         const int total = nbytes * C;
         const long long g0 = (s_lo - J.base_q) * C;
-        for (int g = threadIdx.x; g < total; g += blockDim.x) {
+        for (int g = tid; g < total; g += nthr) {
             const int qi = g / C, c = g - qi * C;
             const long long q = s_lo + qi;
             unsigned int b = 0;
@@ -211,14 +212,14 @@ struct Emitter {
 };
 
 // Interleaved staging -> global, 16-byte vectors when the destination allows.
-__device__ void copy_out(unsigned char* dst, const unsigned char* src, int nbytes) {
+__device__ void copy_out(unsigned char* dst, const unsigned char* src, int nbytes, int tid, int nthr) {
     if ((((uintptr_t)dst) & 15) == 0) {
         const int nv = nbytes >> 4;
-        for (int i = threadIdx.x; i < nv; i += blockDim.x)
+        for (int i = tid; i < nv; i += nthr)
             reinterpret_cast<uint4*>(dst)[i] = reinterpret_cast<const uint4*>(src)[i];
-        for (int i = (nv << 4) + threadIdx.x; i < nbytes; i += blockDim.x) dst[i] = src[i];
+        for (int i = (nv << 4) + tid; i < nbytes; i += nthr) dst[i] = src[i];
     } else {
-        for (int i = threadIdx.x; i < nbytes; i += blockDim.x) dst[i] = src[i];
+        for (int i = tid; i < nbytes; i += nthr) dst[i] = src[i];
     }
 }
 
@@ -231,88 +232,186 @@ __device__ __forceinline__ void load_lut(double* dst, const double* __restrict__
 // ------------------------------------------------------------------------------------------------
 // Integer-ratio LUT FIR.  Frame k (internal index) ends at byte j = (k+1)*bpo - 1 and is
 //   y_k = fold_{i=0..nt-1} (acc + T_i[B[j-i]]) + T_i[bitrev8(B[j-(2nt-1-i)])]
-// Bytes are fetched as aligned 32-bit shared-memory words and funnel-shifted into 4-byte groups; the
-// mirrored half is bit-reversed 4 bytes at a time with one BREV (which also flips the byte order, so
-// both halves are consumed from the top byte down).
+//
+// The binding unit is the shared-memory crossbar (128 B/clk/SM): 2*nt random 8-byte look-ups per frame.
+// A warp-wide LDS.64 is served as two half-warp wavefronts when its 16 lanes hit 16 distinct bank pairs,
+// but random table indices give ~4.7 wavefronts (ncu, profiles/r01_lutfir_v1_*).  So the tables are laid
+// out bank-aware and the lanes are skewed in time:
+//   * entry (replica r, table i, byte b) sits at b*row + (st[r] + i)*8, i.e. its bank pair depends only on
+//     (r, i), never on the data byte;
+//   * lane (r, c) of a half-warp (R = 16/K replicas x K skews) runs table i at step u = i + c, so at any
+//     step the 16 lanes address 16 different bank pairs: every look-up costs exactly 2 wavefronts;
+//   * the fold order per frame is untouched (each lane still walks i = 0..nt-1), so results stay
+//     bit-exact; the price is K-1 idle steps per frame (guarded: the DADDs are predicated off).
+// Input bytes are fetched as aligned 32-bit words and funnel-shifted into 4-byte groups; the mirrored half
+// is bit-reversed 4 bytes at a time with one BREV (which also flips the byte order, so both halves are
+// consumed from the top byte down).
+//
+// The CTA is warp-specialised: P.nc consumer threads only touch shared memory (LUT, input tile, output
+// staging), the remaining threads stage the next input tile from HBM and copy the previous tile's
+// packed PCM out, over double-buffered tiles -- one __syncthreads per tile.
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ double lutfir_frame(const double* __restrict__ lut, const uint32_t* __restrict__ tw,
-                                               int jr, int nt) {
-    const int a = jr + 1 - 4;                 // first byte of the newest 4-byte group
+struct TileInfo {
+    const DevJob* J;
+    long long f0, s_lo;
+    int nf, nbytes, jr_base;
+};
+
+__device__ __forceinline__ TileInfo lutfir_tile(const KParams& P, unsigned int tile) {
+    TileInfo t;
+    const DevJob& J = find_job(P, tile);
+    t.J = &J;
+    t.f0 = J.f_begin + ((long long)(tile - J.tile_begin) << P.tf_shift);
+    const long long left = J.f_begin + J.f_count - t.f0;
+    t.nf = left < P.TF ? (int)left : P.TF;
+    const long long k0 = t.f0 + (P.h - 1);                        // delay_count = h-1 frames are discarded (A4)
+    const long long q_lo = (k0 + 1) * P.bpo - 2 * P.nt - 16;      // oldest byte any (skewed) lane of the tile touches
+    t.s_lo = q_lo & ~15LL;
+    const long long q_hi = (k0 + t.nf) * P.bpo + 32;
+    t.nbytes = (int)(((q_hi - t.s_lo) + 15) & ~15LL);
+    t.jr_base = (int)(k0 * P.bpo - t.s_lo);                       // frame fl of the tile ends at byte (fl+1)*bpo-1+jr_base
+    return t;
+}
+
+template <int OFF>
+__device__ __forceinline__ double lds_f64(uint32_t saddr) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1+%2];" : "=d"(v) : "r"(saddr), "n"(OFF));
+    return v;
+}
+
+// One step of one lane: byte 3-D of qf / qb selects the row, tp + 8*D is the lane's slot.
+// Guarded steps still issue both look-ups (the addresses stay inside the padded LUT); only the two
+// DADDs are predicated on 0 <= i < nt, so the loads keep their ILP.
+template <bool GUARD, int D>
+__device__ __forceinline__ void lutfir_step(uint32_t row, uint32_t tp, uint32_t qf, uint32_t qb, int i0, int nt, double& acc) {
+    const uint32_t bf = __byte_perm(qf, 0, 0x4443 - D);
+    const uint32_t bb = __byte_perm(qb, 0, 0x4443 - D);
+    const double tf = lds_f64<8 * D>(bf * row + tp);
+    const double tb = lds_f64<8 * D>(bb * row + tp);
+    if (!GUARD) {
+        acc = __dadd_rn(__dadd_rn(acc, tf), tb);
+    } else {
+        asm("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %3, %4;\n\t@p add.rn.f64 %0, %0, %1;\n\t@p add.rn.f64 %0, %0, %2;\n\t}"
+            : "+d"(acc) : "d"(tf), "d"(tb), "r"(i0 + D), "r"(nt));
+    }
+}
+
+template <bool GUARD>
+__device__ __forceinline__ void lutfir_group(uint32_t row, uint32_t tp, uint32_t qf, uint32_t qb, int i0, int nt, double& acc) {
+    lutfir_step<GUARD, 0>(row, tp, qf, qb, i0, nt, acc);
+    lutfir_step<GUARD, 1>(row, tp, qf, qb, i0, nt, acc);
+    lutfir_step<GUARD, 2>(row, tp, qf, qb, i0, nt, acc);
+    lutfir_step<GUARD, 3>(row, tp, qf, qb, i0, nt, acc);
+}
+
+// One frame of one lane.  tw: the channel's input tile as words; jr: tile-relative index of the frame's
+// newest byte; c: the lane's skew; tp0: shared-memory address of the lane's slot at step 0.
+__device__ __forceinline__ double lutfir_frame(const KParams& P, const uint32_t* __restrict__ tw, int jr, int c, uint32_t tp0) {
+    const uint32_t row = (uint32_t)P.lut_row_bytes;
+    const int nt = P.nt;
+    // forward half: step u reads byte jr + c - u  (group g: bytes a-4g .. a-4g+3 with a = jr + c - 3)
+    const int a = jr + c - 3;
     int fw = a >> 2;
     const int fsh = (a & 3) * 8;
     uint32_t f_hi = tw[fw + 1];
-    const int b = jr - (2 * nt - 1);          // oldest byte of the window
+    // mirrored half: step u reads byte jr - (2nt-1) - c + u
+    const int b = jr - (2 * nt - 1) - c;
     int bw = b >> 2;
     const int bsh = (b & 3) * 8;
     uint32_t b_lo = tw[bw];
     double acc = 0.0;
-    const double* T = lut;
-    int i = 0;
-    for (; i + 4 <= nt; i += 4) {
-        const uint32_t f_lo = tw[fw];
-        const uint32_t qf = __funnelshift_r(f_lo, f_hi, fsh);
-        f_hi = f_lo; --fw;
-        const uint32_t b_hi = tw[bw + 1];
-        const uint32_t qb = __brev(__funnelshift_r(b_lo, b_hi, bsh));
-        b_lo = b_hi; ++bw;
-        acc = __dadd_rn(__dadd_rn(acc, T[qf >> 24]), T[qb >> 24]);
-        acc = __dadd_rn(__dadd_rn(acc, T[256 + ((qf >> 16) & 0xFF)]), T[256 + ((qb >> 16) & 0xFF)]);
-        acc = __dadd_rn(__dadd_rn(acc, T[512 + ((qf >> 8) & 0xFF)]), T[512 + ((qb >> 8) & 0xFF)]);
-        acc = __dadd_rn(__dadd_rn(acc, T[768 + (qf & 0xFF)]), T[768 + (qb & 0xFF)]);
-        T += 1024;
+    uint32_t tp = tp0;
+    int i0 = -c;
+    const int gp_lo = P.gp_lo, gp_hi = P.gp_hi, ng = P.ngroups;
+    int g = 0;
+#define D2P_GROUP(GUARDED)                                                         \
+    {                                                                              \
+        const uint32_t f_lo = tw[fw];                                              \
+        const uint32_t qf = __funnelshift_r(f_lo, f_hi, fsh);                      \
+        f_hi = f_lo; --fw;                                                         \
+        const uint32_t b_hi = tw[bw + 1];                                          \
+        const uint32_t qb = __brev(__funnelshift_r(b_lo, b_hi, bsh));              \
+        b_lo = b_hi; ++bw;                                                         \
+        lutfir_group<GUARDED>(row, tp, qf, qb, i0, nt, acc);                        \
+        tp += 32; i0 += 4;                                                         \
     }
-    if (i < nt) {
-        const int rem = nt - i;
-        const uint32_t f_lo = tw[fw];
-        const uint32_t qf = __funnelshift_r(f_lo, f_hi, fsh);
-        const uint32_t b_hi = tw[bw + 1];
-        const uint32_t qb = __brev(__funnelshift_r(b_lo, b_hi, bsh));
-        acc = __dadd_rn(__dadd_rn(acc, T[qf >> 24]), T[qb >> 24]);
-        if (rem > 1) acc = __dadd_rn(__dadd_rn(acc, T[256 + ((qf >> 16) & 0xFF)]), T[256 + ((qb >> 16) & 0xFF)]);
-        if (rem > 2) acc = __dadd_rn(__dadd_rn(acc, T[512 + ((qf >> 8) & 0xFF)]), T[512 + ((qb >> 8) & 0xFF)]);
-    }
+    for (; g < gp_lo; ++g) D2P_GROUP(true)
+#pragma unroll 2
+    for (; g < gp_hi; ++g) D2P_GROUP(false)
+    for (; g < ng; ++g) D2P_GROUP(true)
+#undef D2P_GROUP
     return acc;
 }
 
-__global__ void __launch_bounds__(kMaxThreads) lutfir_kernel(const __grid_constant__ KParams P) {
+__global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_constant__ KParams P) {
     extern __shared__ __align__(16) unsigned char smem[];
-    double* lut = reinterpret_cast<double*>(smem);
-    unsigned char* tiles = smem + (size_t)P.lut_doubles * 8;
-    unsigned char* ostage = tiles + (size_t)P.C * P.tile_stride;
+    const unsigned char* lutb = smem + kLutPad;
+    unsigned char* inbuf = smem + kLutPad + (size_t)P.lut_doubles * 8 + kLutPad;
+    unsigned char* obuf = inbuf + 2 * (size_t)P.in_buf_bytes;
 
-    load_lut(lut, P.lut, P.lut_doubles);
+    const int tid = threadIdx.x;
+    const int nc = P.nc;
+    const bool producer = tid >= nc;
+    const int ptid = tid - nc, np = blockDim.x - nc;
+
+    load_lut(reinterpret_cast<double*>(smem + kLutPad), P.lut, P.lut_doubles);
+
+    // lane geometry of the skewed look-up schedule
+    const int lane16 = tid & 15;
+    const int c = lane16 & (P.lutK - 1);
+    const int r = lane16 / P.lutK;
+    const uint32_t tp0 = (uint32_t)__cvta_generic_to_shared(lutb) + (uint32_t)((P.lut_st[r] - c) * 8);
+
     Emitter em; em.init();
+    const bool staged_out = P.out_format != D2P_DEV_OUT_PLANAR;
+    const size_t fb = (size_t)P.C * P.bps;
 
-    for (unsigned int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x) {
-        const DevJob& J = find_job(P, tile);
-        const long long f0 = J.f_begin + (long long)(tile - J.tile_begin) * P.TF;
-        const long long left = J.f_begin + J.f_count - f0;
-        const int nf = left < P.TF ? (int)left : P.TF;
-        const long long k0 = f0 + (P.h - 1);                       // delay_count = h-1 frames are discarded (A4)
-        const long long q_lo = (k0 + 1) * P.bpo - 2 * P.nt;        // oldest byte any frame of the tile needs
-        const long long s_lo = q_lo & ~15LL;
-        const long long q_hi = (k0 + nf) * P.bpo;
-        const int nbytes = (int)(((q_hi - s_lo) + 15) & ~15LL) + 16;
-
-        __syncthreads();                                           // previous tile fully consumed
-        stage_input(P, J, tiles, s_lo, nbytes);
-        __syncthreads();
-
-        const int items = nf * P.C;
-        for (int item = threadIdx.x; item < items; item += blockDim.x) {
-            const int c = item / nf, fl = item - c * nf;           // a warp walks consecutive frames of one channel
-            const uint32_t* tw = reinterpret_cast<const uint32_t*>(tiles + (size_t)c * P.tile_stride);
-            const int jr = (int)((k0 + fl + 1) * P.bpo - 1 - s_lo);
-            const double y = lutfir_frame(lut, tw, jr, P.nt);
-            em.emit(P, J, ostage, c, f0 + fl, fl, y);
-        }
-        if (P.out_format != D2P_DEV_OUT_PLANAR) {
-            __syncthreads();
-            const size_t fb = (size_t)P.C * P.bps;
-            copy_out(J.out + (size_t)(f0 - J.f_begin) * fb, ostage, (int)(nf * fb));
-        }
+    unsigned int tile = blockIdx.x;
+    if (tile < P.total_tiles && producer) {
+        const TileInfo t = lutfir_tile(P, tile);
+        stage_input(P, *t.J, inbuf, t.s_lo, t.nbytes, ptid, np);
     }
-    em.flush(P);
+    __syncthreads();
+
+    int j = 0;
+    bool have_prev = false;
+    TileInfo prev;
+    for (; tile < P.total_tiles; tile += gridDim.x, ++j) {
+        const int bsel = j & 1;
+        const TileInfo t = lutfir_tile(P, tile);
+        if (producer) {
+            const unsigned int nxt = tile + gridDim.x;
+            if (nxt < P.total_tiles) {
+                const TileInfo tn = lutfir_tile(P, nxt);
+                stage_input(P, *tn.J, inbuf + (size_t)(bsel ^ 1) * P.in_buf_bytes, tn.s_lo, tn.nbytes, ptid, np);
+            }
+            if (have_prev && staged_out)
+                copy_out(prev.J->out + (size_t)(prev.f0 - prev.J->f_begin) * fb, obuf + (size_t)(bsel ^ 1) * P.ostage_bytes,
+                         (int)(prev.nf * fb), ptid, np);
+        } else {
+            const unsigned char* tiles = inbuf + (size_t)bsel * P.in_buf_bytes;
+            unsigned char* ostage = obuf + (size_t)bsel * P.ostage_bytes;
+            const int items = P.C << P.tf_shift;
+            const int bpo = P.bpo;
+            for (int it = tid; it < items; it += nc) {
+                const int ch = it >> P.tf_shift, fl = it & (P.TF - 1);
+                if ((fl & ~31) >= t.nf) continue;                    // whole warp beyond the ragged last tile
+                const bool valid = fl < t.nf;
+                const int flc = valid ? fl : t.nf - 1;
+                const uint32_t* tw = reinterpret_cast<const uint32_t*>(tiles + (size_t)ch * P.tile_stride);
+                const int jr = (flc + 1) * bpo - 1 + t.jr_base;
+                const double y = lutfir_frame(P, tw, jr, c, tp0);
+                if (valid) em.emit(P, *t.J, ostage, ch, t.f0 + fl, fl, y);
+            }
+        }
+        prev = t; have_prev = true;
+        __syncthreads();
+    }
+    if (producer && have_prev && staged_out)
+        copy_out(prev.J->out + (size_t)(prev.f0 - prev.J->f_begin) * fb, obuf + (size_t)((j - 1) & 1) * P.ostage_bytes,
+                 (int)(prev.nf * fb), ptid, np);
+    if (!producer) em.flush(P);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -373,7 +472,7 @@ __global__ void __launch_bounds__(kMaxThreads) lm_kernel(const __grid_constant__
         const int bit_base = (int)(t_first - 31 - 8 * s_lo);        // tile-relative bit of the first window's oldest bit
 
         __syncthreads();
-        stage_input(P, J, tiles, s_lo, nbytes);
+        stage_input(P, J, tiles, s_lo, nbytes, threadIdx.x, blockDim.x);
         __syncthreads();
 
         for (int c = 0; c < P.C; ++c) {
@@ -422,7 +521,7 @@ __global__ void __launch_bounds__(kMaxThreads) lm_kernel(const __grid_constant__
         }
         if (P.out_format != D2P_DEV_OUT_PLANAR) {
             const size_t fb = (size_t)P.C * P.bps;
-            copy_out(J.out + (size_t)(f0 - J.f_begin) * fb, ostage, (int)(nf * fb));
+            copy_out(J.out + (size_t)(f0 - J.f_begin) * fb, ostage, (int)(nf * fb), threadIdx.x, blockDim.x);
         }
     }
     em.flush(P);
