@@ -12,7 +12,7 @@ from . import _capi
 from ._capi import Config, D2PError, Job, PlanInfo  # noqa: F401
 
 __all__ = ["make_config", "plan", "frames_for_bytes", "tap_table", "tap_table_names", "device_count",
-           "Converter", "convert_host", "Batch", "D2PError", "HostBuffer"]
+           "Converter", "convert_host", "Batch", "D2PError", "HostBuffer", "total_frames", "block_range"]
 
 
 def make_config(dsd_rate=1, out_rate=352800, filt="E", bits=24, dither="X", level_db=0.0, channels=2,
@@ -46,6 +46,19 @@ def plan(cfg):
 
 def frames_for_bytes(cfg, bytes_per_channel):
     return int(_capi.lib().d2p_frames_for_bytes(C.byref(cfg), int(bytes_per_channel)))
+
+
+def total_frames(cfg, payload_bytes):
+    """Frames per channel a whole container-order payload of `payload_bytes` yields."""
+    return int(_capi.lib().d2p_total_frames(C.byref(cfg), int(payload_bytes)))
+
+
+def block_range(cfg, payload_bytes, first_frame, frame_count):
+    """(in_offset, in_bytes): payload slice that frames [first_frame, first_frame+frame_count) read (halo included)."""
+    off, n = C.c_uint64(), C.c_uint64()
+    _capi.check(_capi.lib().d2p_block_range(C.byref(cfg), int(payload_bytes), int(first_frame), int(frame_count),
+                                            C.byref(off), C.byref(n)))
+    return int(off.value), int(n.value)
 
 
 def tap_table_names():
@@ -181,6 +194,18 @@ class Batch:
     def run(self, jobs, stream=0):
         _capi.check(_capi.lib().d2p_batch_run(self._h, jobs, len(jobs), C.c_void_p(stream)))
         return [int(j.frames) for j in jobs]
+
+    def run_blocks(self, items, stream=0):
+        """items: dicts(d_in, in_offset, in_bytes, payload_bytes, first_frame, frame_count, d_out, out_cap_bytes
+        [, d_f64, f64_stride, dither_seed]) -- time blocks of long payloads (d2p_batch_run_blocks)."""
+        items = list(items)
+        arr = (_capi.BlockJob * len(items))()
+        for j, it in zip(arr, items):
+            for k in ("d_in", "in_offset", "in_bytes", "payload_bytes", "first_frame", "frame_count", "d_out", "out_cap_bytes"):
+                setattr(j, k, it[k])
+            j.d_f64, j.f64_stride = it.get("d_f64", None), it.get("f64_stride", 0)
+            j.dither_seed = it.get("dither_seed", 0)
+        _capi.check(_capi.lib().d2p_batch_run_blocks(self._h, arr, len(items), C.c_void_p(stream)))
 
     def convert_host(self, raw, out):
         """raw/out: uint8 numpy views of host memory (ideally HostBuffer.array).  Returns frames."""

@@ -43,6 +43,14 @@ class Job(C.Structure):
     ]
 
 
+class BlockJob(C.Structure):
+    _fields_ = [
+        ("d_in", C.c_void_p), ("in_offset", C.c_uint64), ("in_bytes", C.c_uint64), ("payload_bytes", C.c_uint64),
+        ("first_frame", C.c_uint64), ("frame_count", C.c_uint64), ("d_out", C.c_void_p), ("out_cap_bytes", C.c_uint64),
+        ("d_f64", C.c_void_p), ("f64_stride", C.c_uint64), ("dither_seed", C.c_uint64),
+    ]
+
+
 # every symbol include/dsd2pcm_b200.h declares
 EXPORTS = [
     "d2p_abi_version", "d2p_strerror", "d2p_last_error", "d2p_device_count",
@@ -50,7 +58,7 @@ EXPORTS = [
     "d2p_create", "d2p_destroy", "d2p_push", "d2p_finish", "d2p_frames_ready", "d2p_pull", "d2p_pull_f64", "d2p_stats",
     "d2p_convert_host", "d2p_host_alloc", "d2p_host_free",
     "d2p_batch_create", "d2p_batch_destroy", "d2p_batch_run", "d2p_batch_convert_host", "d2p_batch_launches",
-    "d2p_batch_stats",
+    "d2p_batch_stats", "d2p_total_frames", "d2p_block_range", "d2p_batch_run_blocks",
 ]
 
 _lib = None
@@ -100,6 +108,10 @@ def lib():
     L.d2p_batch_launches.restype = C.c_uint64
     L.d2p_batch_launches.argtypes = [vp]
     L.d2p_batch_stats.argtypes = [vp, vp, C.POINTER(C.c_int64), C.POINTER(C.c_double)]
+    L.d2p_total_frames.restype = C.c_uint64
+    L.d2p_total_frames.argtypes = [cfgp, C.c_uint64]
+    L.d2p_block_range.argtypes = [cfgp, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    L.d2p_batch_run_blocks.argtypes = [vp, C.POINTER(BlockJob), C.c_int, vp]
     _lib = L
     return L
 

@@ -305,6 +305,34 @@ static unsigned long long seq_index(const Plan& p, int ch, long long f, long lon
     return (unsigned long long)(p.cfg.channels * f_before + (long long)ch * (f_after - f_before) + (f - f_before));
 }
 
+
+// Geometry of a container-order payload: block groups, ragged tail, per-channel length.
+struct PayloadGeom { size_t G; long long unit, groups, tail_per, total_q; bool planar; };
+static PayloadGeom payload_geom(const d2p_config& c, uint64_t payload_bytes) {
+    PayloadGeom g;
+    g.planar = c.in_layout == D2P_LAYOUT_PLANAR;
+    g.G = g.planar ? (size_t)c.channels * c.block_size : (size_t)c.channels;
+    g.unit = g.planar ? (long long)c.block_size : 1;
+    g.groups = (long long)(payload_bytes / g.G);
+    g.tail_per = (long long)((payload_bytes - (size_t)g.groups * g.G) / c.channels);
+    g.total_q = g.groups * g.unit + g.tail_per;
+    return g;
+}
+
+// Slice of the payload that frames [f0, f0+cnt) read: groups [gk, g1) (+ the ragged tail if with_tail).
+static void block_slice(const Plan& p, const PayloadGeom& g, long long f0, long long cnt, long long* gk, long long* g1,
+                        bool* with_tail) {
+    long long k = p.first_byte_needed(f0) / g.unit;
+    if (!g.planar) k = (k / 16) * 16;                           // keep 16-byte vector alignment per channel run
+    if (k > g.groups) k = g.groups;
+    const long long need_q = p.bytes_needed_for_frames(f0 + cnt);
+    long long e = (need_q + g.unit - 1) / g.unit;
+    *with_tail = need_q > g.groups * g.unit;
+    if (e > g.groups) e = g.groups;
+    if (e < k) e = k;
+    *gk = k; *g1 = e;
+}
+
 }  // namespace d2p
 
 using namespace d2p;
@@ -843,6 +871,65 @@ int d2p_batch_run(d2p_batch* b, d2p_job* jobs, int njobs, void* cuda_stream) {
         j.f64 = u.d_f64; j.f64_stride = (long long)u.f64_stride;
         j.seed = u.dither_seed;
         u.frames = (uint64_t)nf;
+    }
+    return b->launcher.run(*b->dp, dj, (cudaStream_t)cuda_stream);
+}
+
+
+// ---- time-block split ----------------------------------------------------------------------------------
+uint64_t d2p_total_frames(const d2p_config* cfg, uint64_t payload_bytes) {
+    if (!cfg) return 0;
+    Plan p; std::string msg;
+    if (make_plan(*cfg, &p, &msg) != D2P_OK) { g_last_error = msg; return 0; }
+    return (uint64_t)p.frames_for_bytes(payload_geom(*cfg, payload_bytes).total_q);
+}
+
+int d2p_block_range(const d2p_config* cfg, uint64_t payload_bytes, uint64_t first_frame, uint64_t frame_count,
+                    uint64_t* in_offset, uint64_t* in_bytes) {
+    if (!cfg || !in_offset || !in_bytes) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    Plan p; std::string msg;
+    int st = make_plan(*cfg, &p, &msg);
+    if (st != D2P_OK) return set_err(st, msg);
+    const PayloadGeom g = payload_geom(*cfg, payload_bytes);
+    const long long total = p.frames_for_bytes(g.total_q);
+    if ((long long)(first_frame + frame_count) > total) return set_err(D2P_ERR_INVALID_ARG, "frame range beyond the payload");
+    if (frame_count == 0) { *in_offset = 0; *in_bytes = 0; return D2P_OK; }
+    long long gk, g1; bool tail;
+    block_slice(p, g, (long long)first_frame, (long long)frame_count, &gk, &g1, &tail);
+    *in_offset = (uint64_t)gk * g.G;
+    *in_bytes = (uint64_t)(g1 - gk) * g.G + (tail ? (uint64_t)g.tail_per * cfg->channels : 0);
+    return D2P_OK;
+}
+
+int d2p_batch_run_blocks(d2p_batch* b, const d2p_block_job* jobs, int njobs, void* cuda_stream) {
+    if (!b || (!jobs && njobs)) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    const Plan& p = b->dp->plan;
+    const d2p_config& c = p.cfg;
+    CK(cudaSetDevice(c.device));
+    const size_t fb = (size_t)c.channels * (c.out_format == D2P_OUT_PLANAR_32 ? 4 : p.bps);
+    std::vector<DevJob> dj((size_t)njobs);
+    for (int i = 0; i < njobs; ++i) {
+        const d2p_block_job& u = jobs[i];
+        const PayloadGeom g = payload_geom(c, u.payload_bytes);
+        const long long total = p.frames_for_bytes(g.total_q);
+        if ((long long)(u.first_frame + u.frame_count) > total) return set_err(D2P_ERR_INVALID_ARG, "frame range beyond the payload");
+        DevJob& j = dj[i];
+        std::memset(&j, 0, sizeof j);
+        if (u.frame_count == 0) continue;
+        long long gk, g1; bool tail;
+        block_slice(p, g, (long long)u.first_frame, (long long)u.frame_count, &gk, &g1, &tail);
+        const uint64_t off = (uint64_t)gk * g.G;
+        const uint64_t len = (uint64_t)(g1 - gk) * g.G + (tail ? (uint64_t)g.tail_per * c.channels : 0);
+        if (u.in_offset != off || u.in_bytes < len) return set_err(D2P_ERR_INVALID_ARG, "block input slice does not match d2p_block_range");
+        if ((size_t)u.frame_count * fb > u.out_cap_bytes) return set_err(D2P_ERR_CAPACITY, "job output buffer too small");
+        if (u.d_f64 && u.f64_stride < u.frame_count) return set_err(D2P_ERR_CAPACITY, "job f64 stride too small");
+        j.in = (const uint8_t*)u.d_in; j.base_q = gk * g.unit;
+        j.end_q = tail ? g.total_q : g1 * g.unit;
+        j.tail_q = (g.planar && tail && g.tail_per > 0) ? g.groups * g.unit : LLONG_MAX; j.tail_len = g.tail_per;
+        j.f_begin = (long long)u.first_frame; j.f_count = (long long)u.frame_count;
+        j.out = (uint8_t*)u.d_out; j.out_stride = (long long)u.frame_count;
+        j.f64 = u.d_f64; j.f64_stride = (long long)u.f64_stride;
+        j.seed = u.dither_seed;
     }
     return b->launcher.run(*b->dp, dj, (cudaStream_t)cuda_stream);
 }

@@ -166,6 +166,31 @@ uint64_t d2p_batch_launches(const d2p_batch* b);
 /* Sum over jobs of clipped samples / max |sample*scale| since creation (synchronises the stream). */
 int  d2p_batch_stats(d2p_batch* b, void* cuda_stream, int64_t* clipped_samples, double* peak_abs);
 
+/* ---- time-block split of one long payload -------------------------------------------- */
+/* Every output frame is a pure function of a bounded input window, so a payload can be cut in
+ * output-frame space and each block converted independently (another stream, another GPU).
+ * d2p_total_frames: frames per channel the whole payload yields.
+ * d2p_block_range : the slice [*in_offset, *in_offset + *in_bytes) of the container-order payload that
+ *                   frames [first_frame, first_frame + frame_count) read, filter halo included and
+ *                   aligned to block groups (host only; needs no GPU). */
+uint64_t d2p_total_frames(const d2p_config* cfg, uint64_t payload_bytes);
+int      d2p_block_range(const d2p_config* cfg, uint64_t payload_bytes, uint64_t first_frame, uint64_t frame_count,
+                         uint64_t* in_offset, uint64_t* in_bytes);
+typedef struct d2p_block_job {
+    const void* d_in;          /* device pointer: payload bytes [in_offset, in_offset + in_bytes) */
+    uint64_t    in_offset;     /* as returned by d2p_block_range */
+    uint64_t    in_bytes;
+    uint64_t    payload_bytes; /* length of the whole payload (all channels) */
+    uint64_t    first_frame;   /* absolute frame index of the block's first output frame */
+    uint64_t    frame_count;
+    void*       d_out;         /* device pointer: the block's packed PCM (frame first_frame at offset 0) */
+    uint64_t    out_cap_bytes;
+    double*     d_f64;         /* optional: channels * f64_stride doubles */
+    uint64_t    f64_stride;
+    uint64_t    dither_seed;   /* per-file seed: blocks of one file share it (noise is keyed by absolute frame) */
+} d2p_block_job;
+int  d2p_batch_run_blocks(d2p_batch* b, const d2p_block_job* jobs, int njobs, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

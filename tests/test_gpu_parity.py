@@ -232,3 +232,32 @@ def test_time_block_split_is_exact():
     parts = conv.pull()
     conv.close()
     assert np.array_equal(whole, parts)
+
+
+@pytest.mark.parametrize("kw", [
+    dict(dsd_rate=4, out_rate=352800, bits=24, channels=2, layout="P", lsb_first=True),
+    dict(dsd_rate=4, out_rate=192000, bits=32, channels=2, layout="P", lsb_first=True),
+    dict(dsd_rate=8, out_rate=352800, bits=24, channels=6, layout="I", lsb_first=False),
+    dict(dsd_rate=2, out_rate=96000, bits=20, channels=3, layout="I", lsb_first=True, dither="T"),
+])
+def test_time_blocks_on_device_equal_one_pass(kw):
+    """8e through the C ABI: d2p_block_range + d2p_batch_run_blocks; every block gets ONLY its slice."""
+    torch = pytest.importorskip("torch")
+    from dsd2dxd_b200 import shard
+    C = kw["channels"]
+    raw = np.random.default_rng(17 + C).integers(0, 256, size=C * (30 * 4096 + 777), dtype=np.uint8)
+    cfg = d2p.make_config(dither_seed=4242, **kw)
+    bps = d2p.plan(cfg)["bytes_per_sample"]
+    ref = orclib.convert(raw, want_f64=False, dither_seed=4242, **kw)
+    blocks = shard.split_payload(cfg, raw.size, 7)
+    batch = d2p.Batch(cfg)
+    d_in = [torch.from_numpy(raw[b.in_offset:b.in_offset + b.in_bytes].copy()).cuda() for b in blocks]
+    d_out = [torch.zeros(b.frame_count * C * bps + 16, dtype=torch.uint8, device="cuda") for b in blocks]
+    batch.run_blocks([dict(d_in=i.data_ptr(), in_offset=b.in_offset, in_bytes=b.in_bytes, payload_bytes=raw.size,
+                           first_frame=b.first_frame, frame_count=b.frame_count, d_out=o.data_ptr(),
+                           out_cap_bytes=o.numel(), dither_seed=4242) for b, i, o in zip(blocks, d_in, d_out)],
+                     torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    got = np.concatenate([o.cpu().numpy()[:b.frame_count * C * bps] for b, o in zip(blocks, d_out)])
+    assert np.array_equal(got, ref.pcm)
+    batch.close()
