@@ -75,12 +75,19 @@ static LutLayout make_lut_layout(int nt, int K) {
     return L;
 }
 
+// Zero region in front of the LUT: idle skew steps of a lane read 0.0 at offsets [-15, 15 + 4*ngroups) slots
+// around its first 128 bytes (see LaneLut in d2p_kernels.cu).
+static int lutfir_zpad(int nt, int K) {
+    const int ng = (nt + K - 1 + 3) / 4;
+    return (128 + (15 + 4 * ng) * 8 + 127) / 128 * 128;
+}
+
 static void lutfir_geometry(const Plan& p, const LutLayout& L, int TF, int* tile_stride, int* in_buf, int* ostage, size_t* smem) {
     const int C = p.cfg.channels;
     *tile_stride = (int)round16((size_t)TF * p.bpo + 2 * p.nt + 80) + 16;
     *in_buf = C * *tile_stride;
     *ostage = p.cfg.out_format == D2P_OUT_PLANAR_32 ? 0 : (int)round16((size_t)TF * C * p.bps);
-    *smem = (size_t)2 * kLutPad + (size_t)L.slots * 2048 + 2 * (size_t)*in_buf + 2 * (size_t)*ostage;
+    *smem = (size_t)lutfir_zpad(p.nt, L.K) + (size_t)L.slots * 2048 + 2 * (size_t)*in_buf + 2 * (size_t)*ostage;
 }
 
 static void lm_geometry(const Plan& p, int TF, int* tile_stride, int* s1_cap, int* s2_cap, size_t* smem) {
@@ -120,6 +127,8 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
     KParams& k = dp->kp;
     std::memset(&k, 0, sizeof k);
     k.C = cfg.channels; k.layout = cfg.in_layout; k.lsb_first = cfg.lsb_first ? 1 : 0; k.block_size = (int)cfg.block_size;
+    k.block_shift = -1;
+    if ((cfg.block_size & (cfg.block_size - 1)) == 0) { k.block_shift = 0; while ((1u << k.block_shift) < cfg.block_size) ++k.block_shift; }
     k.bits = cfg.bits; k.bps = p.bps; k.out_format = cfg.out_format; k.dither = cfg.dither;
     k.has_ds = cfg.has_dither_scale ? 1 : 0; k.peak = p.peak;
     k.scale = p.scale; k.neg_scale = p.neg_scale; k.pos_scale = p.pos_scale;
@@ -183,6 +192,8 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
         k.lutK = L.K; k.lut_row_bytes = L.slots * 8;
         for (int r = 0; r < 16; ++r) k.lut_st[r] = r < L.R ? L.st[r] : 0;
         k.ngroups = (p.nt + L.K - 1 + 3) / 4;
+        k.last_steps = p.nt + L.K - 1 - 4 * (k.ngroups - 1);
+        k.zpad_bytes = lutfir_zpad(p.nt, L.K);
         k.gp_lo = (L.K - 1 + 3) / 4;
         k.gp_hi = p.nt / 4;
         if (k.gp_hi < k.gp_lo) k.gp_hi = k.gp_lo;

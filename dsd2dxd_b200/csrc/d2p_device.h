@@ -45,6 +45,7 @@ struct KParams {
 
     // input format (A1)
     int C, layout, lsb_first, block_size;
+    int block_shift;          // log2(block_size) when it is a power of two, else -1
     // writer (A13-A17)
     int bits, bps, out_format, dither, has_ds, peak;
     double scale, neg_scale, pos_scale;
@@ -61,6 +62,8 @@ struct KParams {
     int lutK, lut_row_bytes;
     int lut_st[16];
     int ngroups, gp_lo, gp_hi;   // 4-step groups per frame; [gp_lo, gp_hi) need no activity guard
+    int last_steps;              // steps of the last group that any lane still needs (1..4)
+    int zpad_bytes;              // zero region in front of the LUT (idle skew steps read 0.0 from it)
     int tf_shift;                // TF == 1 << tf_shift on the integer path
     int nc;                      // consumer threads (the remaining threads of the CTA stage tiles)
     int in_buf_bytes, ostage_bytes;   // per buffer (both are double-buffered)

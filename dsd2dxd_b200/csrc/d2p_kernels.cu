@@ -67,9 +67,73 @@ __device__ __forceinline__ const DevJob& find_job(const KParams& P, unsigned int
 __device__ __forceinline__ long long planar_offset(const KParams& P, const DevJob& J, int c, long long q) {
     if (q >= J.tail_q) return (J.tail_q - J.base_q) * P.C + (long long)c * J.tail_len + (q - J.tail_q);
     const long long qr = q - J.base_q;
-    const long long blk = qr / P.block_size;
+    long long blk;
+    if (P.block_shift >= 0) blk = qr >> P.block_shift;          // 4096 (DSF) and every power of two: no 64-bit division
+    else blk = qr / P.block_size;
     const long long within = qr - blk * P.block_size;
     return (blk * P.C + c) * (long long)P.block_size + within;
+}
+
+// Byte-interleaved payload (DFF / raw -f I): frame-byte q of channel c sits at global byte (q - base_q)*C + c.
+// One work item = 4 consecutive stream bytes of ALL channels = 4*C contiguous global bytes: loaded as C
+// aligned words (consecutive threads -> consecutive chunks, coalesced), transposed in registers into one
+// word per channel, bit-reversed if the source is MSB-first, stored as one word per channel tile.
+// CT = 0: generic (any channel count / unaligned source), byte-wise.
+template <int CT>
+__device__ void stage_interleaved(const KParams& P, const DevJob& J, unsigned char* tiles, long long s_lo, int nbytes,
+                                  int tid, int nthr) {
+    const int C = P.C;
+    const long long g0 = (s_lo - J.base_q) * C;
+    if (CT > 0 && ((((uintptr_t)J.in) & 3) == 0) && ((g0 & 3) == 0)) {
+        const int nquad = nbytes >> 2;
+        for (int w = tid; w < nquad; w += nthr) {
+            const long long q = s_lo + 4LL * w;
+            uint32_t O[CT > 0 ? CT : 1];
+            if (q >= J.base_q && q >= 0 && q + 4 <= J.end_q) {
+                uint32_t W[CT > 0 ? CT : 1];
+                const uint32_t* src = reinterpret_cast<const uint32_t*>(J.in + g0 + 4LL * w * CT);
+#pragma unroll
+                for (int i = 0; i < CT; ++i) W[i] = __ldg(src + i);
+#pragma unroll
+                for (int c = 0; c < CT; ++c) {
+                    uint32_t o = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int k = c + CT * j;
+                        o |= ((W[k >> 2] >> (8 * (k & 3))) & 0xFFu) << (8 * j);
+                    }
+                    O[c] = o;
+                }
+            } else {
+#pragma unroll
+                for (int c = 0; c < CT; ++c) O[c] = 0;
+                if (q + 4 > 0 && q + 4 > J.base_q && q < J.end_q) {
+                    for (int j = 0; j < 4; ++j) {
+                        const long long qq = q + j;
+                        if (qq >= 0 && qq >= J.base_q && qq < J.end_q) {
+#pragma unroll
+                            for (int c = 0; c < CT; ++c) O[c] |= (uint32_t)J.in[(qq - J.base_q) * CT + c] << (8 * j);
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < CT; ++c) {
+                const uint32_t o = P.lsb_first ? O[c] : bitrev_each_byte(O[c]);
+                *reinterpret_cast<uint32_t*>(tiles + (size_t)c * P.tile_stride + 4 * w) = o;
+            }
+        }
+        return;
+    }
+    const int total = nbytes * C;
+    for (int g = tid; g < total; g += nthr) {
+        const int qi = g / C, c = g - qi * C;
+        const long long q = s_lo + qi;
+        unsigned int b = 0;
+        if (q >= 0 && q >= J.base_q && q < J.end_q) b = J.in[g0 + g];
+        if (!P.lsb_first) b = __brev(b) >> 24;
+        tiles[(size_t)c * P.tile_stride + qi] = (unsigned char)b;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -105,16 +169,16 @@ __device__ void stage_input(const KParams& P, const DevJob& J, unsigned char* ti
             *reinterpret_cast<uint4*>(tiles + (size_t)c * P.tile_stride + 16 * idx) = val;
         }
     } else {
-        // byte-interleaved: consecutive threads read consecutive global bytes (coalesced), scatter to C tiles
-        const int total = nbytes * C;
-        const long long g0 = (s_lo - J.base_q) * C;
-        for (int g = tid; g < total; g += nthr) {
-            const int qi = g / C, c = g - qi * C;
-            const long long q = s_lo + qi;
-            unsigned int b = 0;
-            if (q >= 0 && q >= J.base_q && q < J.end_q) b = J.in[g0 + g];
-            if (!P.lsb_first) b = __brev(b) >> 24;
-            tiles[(size_t)c * P.tile_stride + qi] = (unsigned char)b;
+        switch (C) {
+        case 1: stage_interleaved<1>(P, J, tiles, s_lo, nbytes, tid, nthr); break;
+        case 2: stage_interleaved<2>(P, J, tiles, s_lo, nbytes, tid, nthr); break;
+        case 3: stage_interleaved<3>(P, J, tiles, s_lo, nbytes, tid, nthr); break;
+        case 4: stage_interleaved<4>(P, J, tiles, s_lo, nbytes, tid, nthr); break;
+        case 5: stage_interleaved<5>(P, J, tiles, s_lo, nbytes, tid, nthr); break;
+        case 6: stage_interleaved<6>(P, J, tiles, s_lo, nbytes, tid, nthr); break;
+        case 7: stage_interleaved<7>(P, J, tiles, s_lo, nbytes, tid, nthr); break;
+        case 8: stage_interleaved<8>(P, J, tiles, s_lo, nbytes, tid, nthr); break;
+        default: stage_interleaved<0>(P, J, tiles, s_lo, nbytes, tid, nthr); break;
         }
     }
 }
@@ -173,7 +237,7 @@ struct Emitter {
             return;
         }
         // quantize / my_round / clamp_value   rd/pcm_writer.rs:678-705
-        const double r = s < 0.0 ? floor(__dsub_rn(s, 0.5)) : floor(__dadd_rn(s, 0.5));
+        const double r = floor(__dadd_rn(s, s < 0.0 ? -0.5 : 0.5));   // x - 0.5 == x + (-0.5) exactly
         int v = (int)(long long)__double2ll_rz(r);              // f64 -> i64 saturating (NaN -> 0), then i64 -> i32 wrapping
         const int mn = -P.peak, mx = P.peak - 1;
         if (v < mn) { v = mn; clip_event(P, J, ch, f, 0); }
@@ -280,74 +344,120 @@ __device__ __forceinline__ double lds_f64(uint32_t saddr) {
     return v;
 }
 
-// One step of one lane: byte 3-D of qf / qb selects the row, tp + 8*D is the lane's slot.
-// Guarded steps still issue both look-ups (the addresses stay inside the padded LUT); only the two
-// DADDs are predicated on 0 <= i < nt, so the loads keep their ILP.
+// Per-lane constants of the look-up schedule.
+//   rlo / rhi : LUT row pitch in the low / high 16 bits: IDP.2A (dp2a) then extracts one byte of a data word,
+//               multiplies it by the pitch and adds the lane's slot address in ONE instruction
+//               (bytes 3,2 of the word: dp2a.hi with rhi / rlo; bytes 1,0: dp2a.lo with rhi / rlo);
+//   dz        : distance from the lane's LUT slot to its slot in the zero region.  An idle (skew) step uses
+//               pitch 0 and slot + dz: it reads 0.0 from the SAME bank pair the live look-up would have
+//               hit, so idle lanes never add wavefronts, and acc + 0.0 == acc exactly (acc is never -0.0:
+//               it starts at +0.0 and x + y is -0.0 only if both are).
+struct LaneLut { uint32_t rlo, rhi; int dz; };
+
 template <bool GUARD, int D>
-__device__ __forceinline__ void lutfir_step(uint32_t row, uint32_t tp, uint32_t qf, uint32_t qb, int i0, int nt, double& acc) {
-    const uint32_t bf = __byte_perm(qf, 0, 0x4443 - D);
-    const uint32_t bb = __byte_perm(qb, 0, 0x4443 - D);
-    const double tf = lds_f64<8 * D>(bf * row + tp);
-    const double tb = lds_f64<8 * D>(bb * row + tp);
-    if (!GUARD) {
-        acc = __dadd_rn(__dadd_rn(acc, tf), tb);
-    } else {
-        asm("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %3, %4;\n\t@p add.rn.f64 %0, %0, %1;\n\t@p add.rn.f64 %0, %0, %2;\n\t}"
-            : "+d"(acc) : "d"(tf), "d"(tb), "r"(i0 + D), "r"(nt));
+__device__ __forceinline__ void lutfir_step(const LaneLut& L, uint32_t tp, uint32_t qf, uint32_t qb, int i0, int nt, double& acc) {
+    uint32_t rsel = (D & 1) ? L.rlo : L.rhi;
+    uint32_t t = tp;
+    if (GUARD) {
+        const bool live = (unsigned)(i0 + D) < (unsigned)nt;
+        rsel = live ? rsel : 0u;
+        t = live ? tp : tp + (uint32_t)L.dz;
     }
+    const uint32_t af = D < 2 ? __dp2a_hi(rsel, qf, t) : __dp2a_lo(rsel, qf, t);
+    const uint32_t ab = D < 2 ? __dp2a_hi(rsel, qb, t) : __dp2a_lo(rsel, qb, t);
+    const double tf = lds_f64<8 * D>(af);
+    const double tb = lds_f64<8 * D>(ab);
+    acc = __dadd_rn(__dadd_rn(acc, tf), tb);
 }
 
 template <bool GUARD>
-__device__ __forceinline__ void lutfir_group(uint32_t row, uint32_t tp, uint32_t qf, uint32_t qb, int i0, int nt, double& acc) {
-    lutfir_step<GUARD, 0>(row, tp, qf, qb, i0, nt, acc);
-    lutfir_step<GUARD, 1>(row, tp, qf, qb, i0, nt, acc);
-    lutfir_step<GUARD, 2>(row, tp, qf, qb, i0, nt, acc);
-    lutfir_step<GUARD, 3>(row, tp, qf, qb, i0, nt, acc);
+__device__ __forceinline__ void lutfir_group(const LaneLut& L, uint32_t tp, uint32_t qf, uint32_t qb, int i0, int nt, double& acc) {
+    lutfir_step<GUARD, 0>(L, tp, qf, qb, i0, nt, acc);
+    lutfir_step<GUARD, 1>(L, tp, qf, qb, i0, nt, acc);
+    lutfir_step<GUARD, 2>(L, tp, qf, qb, i0, nt, acc);
+    lutfir_step<GUARD, 3>(L, tp, qf, qb, i0, nt, acc);
 }
 
-// One frame of one lane.  tw: the channel's input tile as words; jr: tile-relative index of the frame's
-// newest byte; c: the lane's skew; tp0: shared-memory address of the lane's slot at step 0.
-__device__ __forceinline__ double lutfir_frame(const KParams& P, const uint32_t* __restrict__ tw, int jr, int c, uint32_t tp0) {
-    const uint32_t row = (uint32_t)P.lut_row_bytes;
+// Two frames (A, B) of one lane in lockstep.  Both frames sit at the same table index at every step, so
+// the skew guard, the slot address and the loop bookkeeping are paid once per pair, and the two dependent
+// DADD chains interleave (ILP 2).  B's bytes are A's bytes dW words further on (same byte alignment).
+// tw: A's channel tile as words; jr: tile-relative index of A's newest byte; c: the lane's skew;
+// tp0: shared-memory address of the lane's slot at step 0.
+__device__ __forceinline__ void lutfir_pair(const KParams& P, const LaneLut& L, const uint32_t* __restrict__ tw, int dW,
+                                            int jr, int c, uint32_t tp0, double& yA, double& yB) {
     const int nt = P.nt;
     // forward half: step u reads byte jr + c - u  (group g: bytes a-4g .. a-4g+3 with a = jr + c - 3)
     const int a = jr + c - 3;
-    int fw = a >> 2;
+    const uint32_t* pf = tw + (a >> 2);
     const int fsh = (a & 3) * 8;
-    uint32_t f_hi = tw[fw + 1];
+    uint32_t fhA = pf[1], fhB = pf[1 + dW];
     // mirrored half: step u reads byte jr - (2nt-1) - c + u
     const int b = jr - (2 * nt - 1) - c;
-    int bw = b >> 2;
+    const uint32_t* pb = tw + (b >> 2);
     const int bsh = (b & 3) * 8;
-    uint32_t b_lo = tw[bw];
-    double acc = 0.0;
+    uint32_t blA = pb[0], blB = pb[dW];
+    double accA = 0.0, accB = 0.0;
     uint32_t tp = tp0;
     int i0 = -c;
     const int gp_lo = P.gp_lo, gp_hi = P.gp_hi, ng = P.ngroups;
     int g = 0;
-#define D2P_GROUP(GUARDED)                                                         \
+#define D2P_FETCH()                                                                \
+        const uint32_t flA = pf[0], flB = pf[dW];                                  \
+        const uint32_t qfA = __funnelshift_r(flA, fhA, fsh);                       \
+        const uint32_t qfB = __funnelshift_r(flB, fhB, fsh);                       \
+        fhA = flA; fhB = flB; --pf;                                                \
+        const uint32_t bhA = pb[1], bhB = pb[1 + dW];                              \
+        const uint32_t qbA = __brev(__funnelshift_r(blA, bhA, bsh));               \
+        const uint32_t qbB = __brev(__funnelshift_r(blB, bhB, bsh));               \
+        blA = bhA; blB = bhB; ++pb;
+#define D2P_STEP(GUARD, D)                                                         \
     {                                                                              \
-        const uint32_t f_lo = tw[fw];                                              \
-        const uint32_t qf = __funnelshift_r(f_lo, f_hi, fsh);                      \
-        f_hi = f_lo; --fw;                                                         \
-        const uint32_t b_hi = tw[bw + 1];                                          \
-        const uint32_t qb = __brev(__funnelshift_r(b_lo, b_hi, bsh));              \
-        b_lo = b_hi; ++bw;                                                         \
-        lutfir_group<GUARDED>(row, tp, qf, qb, i0, nt, acc);                        \
+        uint32_t rsel = ((D) & 1) ? L.rlo : L.rhi;                                 \
+        uint32_t t = tp;                                                           \
+        if (GUARD) {                                                               \
+            const bool live = (unsigned)(i0 + (D)) < (unsigned)nt;                 \
+            rsel = live ? rsel : 0u;                                               \
+            t = live ? tp : tp + (uint32_t)L.dz;                                   \
+        }                                                                          \
+        const uint32_t afA = (D) < 2 ? __dp2a_hi(rsel, qfA, t) : __dp2a_lo(rsel, qfA, t);   \
+        const uint32_t abA = (D) < 2 ? __dp2a_hi(rsel, qbA, t) : __dp2a_lo(rsel, qbA, t);   \
+        const uint32_t afB = (D) < 2 ? __dp2a_hi(rsel, qfB, t) : __dp2a_lo(rsel, qfB, t);   \
+        const uint32_t abB = (D) < 2 ? __dp2a_hi(rsel, qbB, t) : __dp2a_lo(rsel, qbB, t);   \
+        const double tfA = lds_f64<8 * (D)>(afA), tbA = lds_f64<8 * (D)>(abA);     \
+        const double tfB = lds_f64<8 * (D)>(afB), tbB = lds_f64<8 * (D)>(abB);     \
+        accA = __dadd_rn(__dadd_rn(accA, tfA), tbA);                               \
+        accB = __dadd_rn(__dadd_rn(accB, tfB), tbB);                               \
+    }
+#define D2P_GROUP(GUARD)                                                           \
+    {                                                                              \
+        D2P_FETCH()                                                                \
+        D2P_STEP(GUARD, 0) D2P_STEP(GUARD, 1) D2P_STEP(GUARD, 2) D2P_STEP(GUARD, 3) \
         tp += 32; i0 += 4;                                                         \
     }
     for (; g < gp_lo; ++g) D2P_GROUP(true)
-#pragma unroll 2
+#pragma unroll 1
     for (; g < gp_hi; ++g) D2P_GROUP(false)
-    for (; g < ng; ++g) D2P_GROUP(true)
+    for (; g < ng - 1; ++g) D2P_GROUP(true)
+    if (g < ng) {
+        // last group: steps beyond nt + K - 1 are idle for every lane and are not issued at all
+        D2P_FETCH()
+        const int ls = P.last_steps;
+        D2P_STEP(true, 0)
+        if (ls > 1) D2P_STEP(true, 1)
+        if (ls > 2) D2P_STEP(true, 2)
+        if (ls > 3) D2P_STEP(true, 3)
+    }
 #undef D2P_GROUP
-    return acc;
+#undef D2P_STEP
+#undef D2P_FETCH
+    yA = accA; yB = accB;
 }
 
 __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_constant__ KParams P) {
     extern __shared__ __align__(16) unsigned char smem[];
-    const unsigned char* lutb = smem + kLutPad;
-    unsigned char* inbuf = smem + kLutPad + (size_t)P.lut_doubles * 8 + kLutPad;
+    // [zero region | LUT | 2 input tiles | 2 output stages]
+    const unsigned char* lutb = smem + P.zpad_bytes;
+    unsigned char* inbuf = smem + P.zpad_bytes + (size_t)P.lut_doubles * 8;
     unsigned char* obuf = inbuf + 2 * (size_t)P.in_buf_bytes;
 
     const int tid = threadIdx.x;
@@ -355,13 +465,18 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
     const bool producer = tid >= nc;
     const int ptid = tid - nc, np = blockDim.x - nc;
 
-    load_lut(reinterpret_cast<double*>(smem + kLutPad), P.lut, P.lut_doubles);
+    for (int i = tid; i < (P.zpad_bytes >> 3); i += blockDim.x) reinterpret_cast<double*>(smem)[i] = 0.0;
+    load_lut(reinterpret_cast<double*>(smem + P.zpad_bytes), P.lut, P.lut_doubles);
 
     // lane geometry of the skewed look-up schedule
     const int lane16 = tid & 15;
     const int c = lane16 & (P.lutK - 1);
     const int r = lane16 / P.lutK;
     const uint32_t tp0 = (uint32_t)__cvta_generic_to_shared(lutb) + (uint32_t)((P.lut_st[r] - c) * 8);
+    LaneLut LL;
+    LL.rlo = (uint32_t)P.lut_row_bytes;
+    LL.rhi = (uint32_t)P.lut_row_bytes << 16;
+    LL.dz = 128 - P.zpad_bytes - (P.lut_st[r] & ~15) * 8;       // same bank pair, inside the zero region
 
     Emitter em; em.init();
     const bool staged_out = P.out_format != D2P_DEV_OUT_PLANAR;
@@ -394,15 +509,22 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
             unsigned char* ostage = obuf + (size_t)bsel * P.ostage_bytes;
             const int items = P.C << P.tf_shift;
             const int bpo = P.bpo;
-            for (int it = tid; it < items; it += nc) {
+            // a lane runs frames A = item `it` and B = item `it + nc` together: B is nc frames later in the same
+            // channel (TF >= 2 nc) or the same frame of a later channel -- either way a fixed word offset.
+            const int dW = P.TF >= 2 * nc ? (nc * bpo) >> 2 : ((nc > P.TF ? nc >> P.tf_shift : 1) * P.tile_stride) >> 2;
+            for (int it = tid; it < items; it += 2 * nc) {
                 const int ch = it >> P.tf_shift, fl = it & (P.TF - 1);
-                if ((fl & ~31) >= t.nf) continue;                    // whole warp beyond the ragged last tile
-                const bool valid = fl < t.nf;
-                const int flc = valid ? fl : t.nf - 1;
+                const int itB = it + nc;
+                const bool hasB = itB < items;
+                const int chB = itB >> P.tf_shift, flB = itB & (P.TF - 1);
+                const bool liveA = (fl & ~31) < t.nf, liveB = hasB && (flB & ~31) < t.nf;   // warp-uniform
+                if (!liveA && !liveB) continue;                      // whole warp beyond the ragged last tile
                 const uint32_t* tw = reinterpret_cast<const uint32_t*>(tiles + (size_t)ch * P.tile_stride);
-                const int jr = (flc + 1) * bpo - 1 + t.jr_base;
-                const double y = lutfir_frame(P, tw, jr, c, tp0);
-                if (valid) em.emit(P, *t.J, ostage, ch, t.f0 + fl, fl, y);
+                const int jr = (fl + 1) * bpo - 1 + t.jr_base;
+                double yA, yB;
+                lutfir_pair(P, LL, tw, hasB ? dW : 0, jr, c, tp0, yA, yB);
+                if (fl < t.nf) em.emit(P, *t.J, ostage, ch, t.f0 + fl, fl, yA);
+                if (hasB && flB < t.nf) em.emit(P, *t.J, ostage, chB, t.f0 + flB, flB, yB);
             }
         }
         prev = t; have_prev = true;

@@ -13,7 +13,7 @@ namespace d2p {
 static const int kMaxThreads = 512;          // CTA size of lm_kernel; consumer threads of lutfir_kernel
 static const int kLutfirProducers = 128;     // extra threads of lutfir_kernel that stage tiles and copy results out
 static const int kLutfirThreads = kMaxThreads + kLutfirProducers;
-static const int kLutPad = 128;              // bytes before/after the LUT in shared memory (guarded look-ups may stray)
+static const int kLutPad = 128;              // legacy pad constant (lm_kernel does not use it)
 static const int kMaxSmem = 227 * 1024;      // opt-in dynamic shared memory per CTA on sm_100a
 
 const char* kernel_name(bool lm);
