@@ -48,6 +48,7 @@ struct KParams {
     int block_shift;          // log2(block_size) when it is a power of two, else -1
     // writer (A13-A17)
     int bits, bps, out_format, dither, has_ds, peak;
+    int shl20;                // 4 for 20-bit output (left-aligned in its 3-byte container), else 0
     double scale, neg_scale, pos_scale;
 
     int TF;                   // output frames per tile

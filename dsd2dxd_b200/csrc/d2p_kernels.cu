@@ -35,23 +35,31 @@ __device__ __forceinline__ uint32_t bitrev_each_byte(uint32_t w) {   // MSB-firs
     return __byte_perm(__brev(w), 0, 0x0123);
 }
 
-// Philox4x32-10 (Salmon et al. 2011): counter-based noise keyed by (seed; frame, channel).
-__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
-                                              uint32_t k0, uint32_t k1, uint32_t out[4]) {
-    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+// Philox2x32-10 (Salmon et al., SC'11): counter-based noise keyed by (seed; frame, channel).  Two 32-bit
+// words per sample are all TPDF / rectangular dither need (same definition as oracle/oracle.cpp).
+__device__ __forceinline__ void philox2x32_10(unsigned long long frame, uint32_t chan, uint32_t key, uint32_t& a, uint32_t& b) {
+    const uint32_t M = 0xD256D193u, W = 0x9E3779B9u;
+    uint32_t c0 = (uint32_t)frame, c1 = ((uint32_t)(frame >> 32) << 8) ^ chan;
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
-        const uint32_t hi0 = __umulhi(M0, c0), lo0 = M0 * c0;
-        const uint32_t hi1 = __umulhi(M1, c2), lo1 = M1 * c2;
-        const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
-        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
-        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+        const uint32_t hi = __umulhi(M, c0), lo = M * c0;
+        c0 = hi ^ key ^ c1; c1 = lo;
+        key += W;
     }
-    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+    a = c0; b = c1;
 }
-__device__ __forceinline__ double u53(uint32_t hi, uint32_t lo) {
-    const unsigned long long u = ((unsigned long long)hi << 32) | lo;
-    return __dmul_rn((double)(u >> 11), 1.0 / 9007199254740992.0);
+__device__ __forceinline__ uint32_t philox_key(unsigned long long seed) {
+    return (uint32_t)seed ^ ((uint32_t)(seed >> 32) * 0x85EBCA6Bu);
+}
+// (double)u for a 32-bit u without a conversion instruction: 2^52 + u is exact, differences too
+__device__ __forceinline__ double u32_as_2p52(uint32_t u) { return __hiloint2double(0x43300000, (int)u); }
+__device__ __forceinline__ double dither_noise(int kind, unsigned long long frame, uint32_t chan, uint32_t key) {
+    uint32_t a, b;
+    philox2x32_10(frame, chan, key, a, b);
+    if (kind == 'T')      // r1 - r2 with r = u * 2^-33 in [0, 0.5): the difference of the integers is exact
+        return __dmul_rn(__dsub_rn(u32_as_2p52(a), u32_as_2p52(b)), 1.0 / 8589934592.0);
+    const unsigned long long u = (((unsigned long long)a << 32) | b) >> 11;   // 53 bits -> [0,1)
+    return __dsub_rn(__dmul_rn((double)u, 1.0 / 9007199254740992.0), 0.5);
 }
 
 __device__ __forceinline__ const DevJob& find_job(const KParams& P, unsigned int tile) {
@@ -186,11 +194,18 @@ __device__ void stage_input(const KParams& P, const DevJob& J, unsigned char* ti
 // ------------------------------------------------------------------------------------------------
 // A13-A17: scale -> dither -> quantise -> pack, plus the level / clip statistics.
 // ------------------------------------------------------------------------------------------------
+// WM (writer mode): 0 = generic (every option, decided at run time);
+//   1 = the common file/stdout case decided on the host: 3-byte little-endian interleaved integers (20/24 bit),
+//       no f64 side output, no DSD2DXD_DITHERSCALE, |sample*scale| provably < 2^31 - 1;  DITH = 0 / 'T' / 'R'
+//       is then a compile-time constant too.
+template <int WM, int DITH>
 struct Emitter {
-    double peak;
+    unsigned long long peakb;          // max |sample*scale| as f64 bits (non-negative doubles order as integers)
     unsigned int clip_lo, clip_hi;
+    uint32_t key;
 
-    __device__ __forceinline__ void init() { peak = 0.0; clip_lo = 0; clip_hi = 0; }
+    __device__ __forceinline__ void init() { peakb = 0ull; clip_lo = 0; clip_hi = 0; key = 0; }
+    __device__ __forceinline__ void set_job(const DevJob& J) { key = philox_key(J.seed); }
 
     __device__ __forceinline__ void clip_event(const KParams& P, const DevJob& J, int ch, long long f, int high) {
         if (high) ++clip_hi; else ++clip_lo;
@@ -206,23 +221,29 @@ struct Emitter {
     // y: decimator output of channel ch, absolute frame f; fl: frame index inside the tile
     __device__ __forceinline__ void emit(const KParams& P, const DevJob& J, unsigned char* ostage,
                                          int ch, long long f, int fl, double y) {
+        if (WM == 1) {
+            double s = __dmul_rn(y, P.scale);                   // scale_and_dither  rd/pcm_writer.rs:651
+            const unsigned long long ab = (unsigned long long)__double_as_longlong(fabs(s));
+            peakb = ab > peakb ? ab : peakb;                    // process_levels    rd/conversion_context.rs:235-240
+            if (DITH) s = __dadd_rn(s, dither_noise(DITH, (unsigned long long)f, (uint32_t)ch, key));
+            // quantize / my_round / clamp_value   rd/pcm_writer.rs:678-705 ; floor fused into the conversion
+            int v = __double2int_rd(__dadd_rn(s, s < 0.0 ? -0.5 : 0.5));
+            const int mn = -P.peak, mx = P.peak - 1;
+            if (v < mn) { v = mn; clip_event(P, J, ch, f, 0); }
+            else if (v > mx) { v = mx; clip_event(P, J, ch, f, 1); }
+            const unsigned int u = (unsigned int)v << P.shl20;  // 20-bit: left-aligned in the 3-byte container
+            unsigned char* o = ostage + (fl * P.C + ch) * 3;    // pack_int  rd/pcm_writer.rs:372-396
+            o[0] = (unsigned char)u; o[1] = (unsigned char)(u >> 8); o[2] = (unsigned char)(u >> 16);
+            return;
+        }
         const long long fj = f - J.f_begin;
         if (J.f64) J.f64[(long long)ch * J.f64_stride + fj] = y;
         double s = __dmul_rn(y, P.scale);                       // scale_and_dither  rd/pcm_writer.rs:651
-        peak = fmax(peak, fabs(s));                             // process_levels    rd/conversion_context.rs:235-240
+        const unsigned long long ab = (unsigned long long)__double_as_longlong(fabs(s));
+        peakb = ab > peakb ? ab : peakb;
         if (P.has_ds) s = __dmul_rn(s, P.neg_scale);            // Dither::process_samp rd/dither.rs:86-95
-        if (P.dither == 'T' || P.dither == 'R') {
-            uint32_t r[4];
-            philox4x32_10((uint32_t)f, (uint32_t)((unsigned long long)f >> 32), (uint32_t)ch, 0u,
-                          (uint32_t)J.seed, (uint32_t)(J.seed >> 32), r);
-            if (P.dither == 'T') {
-                const double r1 = __dmul_rn(u53(r[0], r[1]), 0.5);
-                const double r2 = __dmul_rn(u53(r[2], r[3]), 0.5);
-                s = __dadd_rn(s, __dsub_rn(r1, r2));
-            } else {
-                s = __dadd_rn(s, __dsub_rn(u53(r[0], r[1]), 0.5));
-            }
-        }
+        if (P.dither == 'T' || P.dither == 'R')
+            s = __dadd_rn(s, dither_noise(P.dither, (unsigned long long)f, (uint32_t)ch, key));
         if (P.has_ds) s = __dmul_rn(s, P.pos_scale);
 
         if (P.bits == 32) {
@@ -258,8 +279,7 @@ struct Emitter {
     }
 
     __device__ __forceinline__ void flush(const KParams& P) {
-        // non-negative doubles compare like their bit patterns
-        unsigned long long pb = (unsigned long long)__double_as_longlong(peak);
+        unsigned long long pb = peakb;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             const unsigned long long other = __shfl_xor_sync(0xffffffffu, pb, o);
@@ -383,6 +403,8 @@ __device__ __forceinline__ void lutfir_group(const LaneLut& L, uint32_t tp, uint
 // DADD chains interleave (ILP 2).  B's bytes are A's bytes dW words further on (same byte alignment).
 // tw: A's channel tile as words; jr: tile-relative index of A's newest byte; c: the lane's skew;
 // tp0: shared-memory address of the lane's slot at step 0.
+// PAIR = false: frame A alone (tiles too small to give every consumer thread two frames).
+template <bool PAIR>
 __device__ __forceinline__ void lutfir_pair(const KParams& P, const LaneLut& L, const uint32_t* __restrict__ tw, int dW,
                                             int jr, int c, uint32_t tp0, double& yA, double& yB) {
     const int nt = P.nt;
@@ -390,25 +412,25 @@ __device__ __forceinline__ void lutfir_pair(const KParams& P, const LaneLut& L, 
     const int a = jr + c - 3;
     const uint32_t* pf = tw + (a >> 2);
     const int fsh = (a & 3) * 8;
-    uint32_t fhA = pf[1], fhB = pf[1 + dW];
+    uint32_t fhA = pf[1], fhB = PAIR ? pf[1 + dW] : 0u;
     // mirrored half: step u reads byte jr - (2nt-1) - c + u
     const int b = jr - (2 * nt - 1) - c;
     const uint32_t* pb = tw + (b >> 2);
     const int bsh = (b & 3) * 8;
-    uint32_t blA = pb[0], blB = pb[dW];
+    uint32_t blA = pb[0], blB = PAIR ? pb[dW] : 0u;
     double accA = 0.0, accB = 0.0;
     uint32_t tp = tp0;
     int i0 = -c;
     const int gp_lo = P.gp_lo, gp_hi = P.gp_hi, ng = P.ngroups;
     int g = 0;
 #define D2P_FETCH()                                                                \
-        const uint32_t flA = pf[0], flB = pf[dW];                                  \
+        const uint32_t flA = pf[0], flB = PAIR ? pf[dW] : 0u;                      \
         const uint32_t qfA = __funnelshift_r(flA, fhA, fsh);                       \
-        const uint32_t qfB = __funnelshift_r(flB, fhB, fsh);                       \
+        const uint32_t qfB = PAIR ? __funnelshift_r(flB, fhB, fsh) : 0u;           \
         fhA = flA; fhB = flB; --pf;                                                \
-        const uint32_t bhA = pb[1], bhB = pb[1 + dW];                              \
+        const uint32_t bhA = pb[1], bhB = PAIR ? pb[1 + dW] : 0u;                  \
         const uint32_t qbA = __brev(__funnelshift_r(blA, bhA, bsh));               \
-        const uint32_t qbB = __brev(__funnelshift_r(blB, bhB, bsh));               \
+        const uint32_t qbB = PAIR ? __brev(__funnelshift_r(blB, bhB, bsh)) : 0u;   \
         blA = bhA; blB = bhB; ++pb;
 #define D2P_STEP(GUARD, D)                                                         \
     {                                                                              \
@@ -421,12 +443,14 @@ __device__ __forceinline__ void lutfir_pair(const KParams& P, const LaneLut& L, 
         }                                                                          \
         const uint32_t afA = (D) < 2 ? __dp2a_hi(rsel, qfA, t) : __dp2a_lo(rsel, qfA, t);   \
         const uint32_t abA = (D) < 2 ? __dp2a_hi(rsel, qbA, t) : __dp2a_lo(rsel, qbA, t);   \
-        const uint32_t afB = (D) < 2 ? __dp2a_hi(rsel, qfB, t) : __dp2a_lo(rsel, qfB, t);   \
-        const uint32_t abB = (D) < 2 ? __dp2a_hi(rsel, qbB, t) : __dp2a_lo(rsel, qbB, t);   \
         const double tfA = lds_f64<8 * (D)>(afA), tbA = lds_f64<8 * (D)>(abA);     \
-        const double tfB = lds_f64<8 * (D)>(afB), tbB = lds_f64<8 * (D)>(abB);     \
         accA = __dadd_rn(__dadd_rn(accA, tfA), tbA);                               \
-        accB = __dadd_rn(__dadd_rn(accB, tfB), tbB);                               \
+        if (PAIR) {                                                                \
+            const uint32_t afB = (D) < 2 ? __dp2a_hi(rsel, qfB, t) : __dp2a_lo(rsel, qfB, t);   \
+            const uint32_t abB = (D) < 2 ? __dp2a_hi(rsel, qbB, t) : __dp2a_lo(rsel, qbB, t);   \
+            const double tfB = lds_f64<8 * (D)>(afB), tbB = lds_f64<8 * (D)>(abB); \
+            accB = __dadd_rn(__dadd_rn(accB, tfB), tbB);                           \
+        }                                                                          \
     }
 #define D2P_GROUP(GUARD)                                                           \
     {                                                                              \
@@ -453,6 +477,7 @@ __device__ __forceinline__ void lutfir_pair(const KParams& P, const LaneLut& L, 
     yA = accA; yB = accB;
 }
 
+template <int WM, int DITH>
 __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_constant__ KParams P) {
     extern __shared__ __align__(16) unsigned char smem[];
     // [zero region | LUT | 2 input tiles | 2 output stages]
@@ -478,7 +503,7 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
     LL.rhi = (uint32_t)P.lut_row_bytes << 16;
     LL.dz = 128 - P.zpad_bytes - (P.lut_st[r] & ~15) * 8;       // same bank pair, inside the zero region
 
-    Emitter em; em.init();
+    Emitter<WM, DITH> em; em.init();
     const bool staged_out = P.out_format != D2P_DEV_OUT_PLANAR;
     const size_t fb = (size_t)P.C * P.bps;
 
@@ -507,24 +532,41 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
         } else {
             const unsigned char* tiles = inbuf + (size_t)bsel * P.in_buf_bytes;
             unsigned char* ostage = obuf + (size_t)bsel * P.ostage_bytes;
-            const int items = P.C << P.tf_shift;
+            const int items = P.C << P.tf_shift;                  // item = channel * TF + frame-in-tile
             const int bpo = P.bpo;
-            // a lane runs frames A = item `it` and B = item `it + nc` together: B is nc frames later in the same
-            // channel (TF >= 2 nc) or the same frame of a later channel -- either way a fixed word offset.
-            const int dW = P.TF >= 2 * nc ? (nc * bpo) >> 2 : ((nc > P.TF ? nc >> P.tf_shift : 1) * P.tile_stride) >> 2;
-            for (int it = tid; it < items; it += 2 * nc) {
-                const int ch = it >> P.tf_shift, fl = it & (P.TF - 1);
-                const int itB = it + nc;
-                const bool hasB = itB < items;
-                const int chB = itB >> P.tf_shift, flB = itB & (P.TF - 1);
-                const bool liveA = (fl & ~31) < t.nf, liveB = hasB && (flB & ~31) < t.nf;   // warp-uniform
-                if (!liveA && !liveB) continue;                      // whole warp beyond the ragged last tile
-                const uint32_t* tw = reinterpret_cast<const uint32_t*>(tiles + (size_t)ch * P.tile_stride);
-                const int jr = (fl + 1) * bpo - 1 + t.jr_base;
-                double yA, yB;
-                lutfir_pair(P, LL, tw, hasB ? dW : 0, jr, c, tp0, yA, yB);
-                if (fl < t.nf) em.emit(P, *t.J, ostage, ch, t.f0 + fl, fl, yA);
-                if (hasB && flB < t.nf) em.emit(P, *t.J, ostage, chB, t.f0 + flB, flB, yB);
+            em.set_job(*t.J);
+            // Passes over the tile's items.  While at least 2*nc items remain, every consumer thread runs two
+            // frames in lockstep (A = base + tid, B = A + nc); a remainder of more than nc items is split into
+            // two halves the same way; up to nc items run one frame per thread.
+            for (int base = 0; base < items;) {
+                const int rem = items - base;
+                const bool pair = rem > nc;
+                const int ps = rem >= 2 * nc ? nc : (pair ? (((rem + 1) >> 1) + 31) & ~31 : rem);
+                if (tid < ps) {
+                    const int it = base + tid;
+                    const int ch = it >> P.tf_shift, fl = it & (P.TF - 1);
+                    const uint32_t* tw = reinterpret_cast<const uint32_t*>(tiles + (size_t)ch * P.tile_stride);
+                    const int jr = (fl + 1) * bpo - 1 + t.jr_base;
+                    if (pair) {
+                        const int itB = it + ps;
+                        const bool hasB = itB < items;
+                        const int chB = itB >> P.tf_shift, flB = itB & (P.TF - 1);
+                        // warp-uniform: lanes are 32 consecutive frames of an aligned group
+                        if ((fl & ~31) < t.nf || (hasB && (flB & ~31) < t.nf)) {
+                            // B's bytes sit a fixed, word-aligned distance from A's (ps and TF are multiples of 32)
+                            const int dW = hasB ? ((chB - ch) * P.tile_stride + (flB - fl) * bpo) >> 2 : 0;
+                            double yA, yB;
+                            lutfir_pair<true>(P, LL, tw, dW, jr, c, tp0, yA, yB);
+                            if (fl < t.nf) em.emit(P, *t.J, ostage, ch, t.f0 + fl, fl, yA);
+                            if (hasB && flB < t.nf) em.emit(P, *t.J, ostage, chB, t.f0 + flB, flB, yB);
+                        }
+                    } else if ((fl & ~31) < t.nf) {
+                        double yA, yB;
+                        lutfir_pair<false>(P, LL, tw, 0, jr, c, tp0, yA, yB);
+                        if (fl < t.nf) em.emit(P, *t.J, ostage, ch, t.f0 + fl, fl, yA);
+                    }
+                }
+                base += pair ? 2 * ps : ps;
             }
         }
         prev = t; have_prev = true;
@@ -563,10 +605,11 @@ __global__ void __launch_bounds__(kMaxThreads) lm_kernel(const __grid_constant__
     __shared__ unsigned char sgroups[kMaxPhasesDev];
     if (threadIdx.x < kMaxPhasesDev) sgroups[threadIdx.x] = P.groups[threadIdx.x];
     load_lut(lut, P.lut, P.lut_doubles);
-    Emitter em; em.init();
+    Emitter<0, 0> em; em.init();
 
     for (unsigned int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x) {
         const DevJob& J = find_job(P, tile);
+        em.set_job(J);
         const long long f0 = J.f_begin + (long long)(tile - J.tile_begin) * P.TF;
         const long long left = J.f_begin + J.f_count - f0;
         const int nf = left < P.TF ? (int)left : P.TF;
@@ -654,35 +697,50 @@ __global__ void __launch_bounds__(kMaxThreads) lm_kernel(const __grid_constant__
 // ------------------------------------------------------------------------------------------------
 const char* kernel_name(bool lm) { return lm ? "d2p::lm_kernel" : "d2p::lutfir_kernel"; }
 
-static cudaError_t ensure_smem_attr(bool lm) {
-    static bool attr_done[2][64] = {};
+// variant: 0 = lm_kernel, 1 = lutfir generic writer, 2/3/4 = lutfir fast 3-byte-LE writer with dither X/T/R
+static const void* kernel_fn(int variant) {
+    switch (variant) {
+    case 0: return (const void*)lm_kernel;
+    case 2: return (const void*)lutfir_kernel<1, 0>;
+    case 3: return (const void*)lutfir_kernel<1, 'T'>;
+    case 4: return (const void*)lutfir_kernel<1, 'R'>;
+    default: return (const void*)lutfir_kernel<0, 0>;
+    }
+}
+
+int kernel_variant(const KParams& P, bool lm, bool fast_writer_ok) {
+    if (lm) return 0;
+    if (!fast_writer_ok) return 1;
+    return P.dither == 'T' ? 3 : (P.dither == 'R' ? 4 : 2);
+}
+
+static cudaError_t ensure_smem_attr(int variant) {
+    static bool attr_done[5][64] = {};
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
-    const void* fn = lm ? (const void*)lm_kernel : (const void*)lutfir_kernel;
-    if (dev < 64 && !attr_done[lm ? 1 : 0][dev]) {
+    if (dev < 64 && !attr_done[variant][dev]) {
         // the opt-in limit (227 KiB) covers static + dynamic shared memory: leave room for the kernels' statics
-        e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem - 1024);
+        e = cudaFuncSetAttribute(kernel_fn(variant), cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem - 1024);
         if (e != cudaSuccess) { cudaGetLastError(); return e; }
-        attr_done[lm ? 1 : 0][dev] = true;
+        attr_done[variant][dev] = true;
     }
     return cudaSuccess;
 }
 
 int max_ctas_per_sm(bool lm, int threads, size_t smem) {
-    if (ensure_smem_attr(lm) != cudaSuccess) return 0;
+    const int variant = lm ? 0 : 1;
+    if (ensure_smem_attr(variant) != cudaSuccess) return 0;
     int n = 0;
-    const void* fn = lm ? (const void*)lm_kernel : (const void*)lutfir_kernel;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, threads, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel_fn(variant), threads, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
     return n;
 }
 
-cudaError_t launch_kernels(const KParams& P, bool lm, int grid, int threads, size_t smem, cudaStream_t stream) {
-    cudaError_t e = ensure_smem_attr(lm);
+cudaError_t launch_kernels(const KParams& P, int variant, int grid, int threads, size_t smem, cudaStream_t stream) {
+    cudaError_t e = ensure_smem_attr(variant);
     if (e != cudaSuccess) return e;
-    if (lm) lm_kernel<<<grid, threads, smem, stream>>>(P);
-    else lutfir_kernel<<<grid, threads, smem, stream>>>(P);
-    return cudaGetLastError();
+    void* args[] = {(void*)&P};
+    return cudaLaunchKernel(kernel_fn(variant), dim3(grid), dim3(threads), args, smem, stream);
 }
 
 }  // namespace d2p

@@ -18,7 +18,7 @@
  *
  * One deliberate substitution: the reference draws TPDF/rectangular dither and the FPD seed from
  * rand::thread_rng() (OS-seeded, irreproducible: SURVEY.md F5).  Here the noise comes from
- * Philox4x32-10 keyed by (seed, channel, frame) -- the same definition the CUDA path uses -- so that
+ * Philox2x32-10 keyed by (seed; frame, channel) -- the same definition the CUDA path uses -- so that
  * dithered output can be compared exactly as well as within +-1 LSB of the undithered result.
  */
 #include <algorithm>
@@ -525,6 +525,21 @@ Philox philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_
     }
     return Philox{{c0, c1, c2, c3}};
 }
+// Philox2x32-10 (same paper): counter = (frame_lo, frame_hi << 8 | channel), one 32-bit key folded from
+// the 64-bit seed.  Two 32-bit words per sample: all that TPDF / rectangular dither need.
+struct Philox2 { uint32_t a, b; };
+Philox2 philox2x32_10(uint64_t frame, uint32_t chan, uint64_t seed) {
+    const uint32_t M = 0xD256D193u, W = 0x9E3779B9u;
+    uint32_t c0 = (uint32_t)frame, c1 = ((uint32_t)(frame >> 32) << 8) ^ chan;
+    uint32_t k = (uint32_t)seed ^ ((uint32_t)(seed >> 32) * 0x85EBCA6Bu);
+    for (int r = 0; r < 10; ++r) {
+        uint64_t p = (uint64_t)M * c0;
+        uint32_t n0 = (uint32_t)(p >> 32) ^ k ^ c1;
+        c1 = (uint32_t)p; c0 = n0;
+        k += W;
+    }
+    return Philox2{c0, c1};
+}
 inline double u53(uint32_t hi, uint32_t lo) {       // [0,1) with 53 random bits, as rand's Standard f64
     uint64_t u = ((uint64_t)hi << 32) | lo;
     return (double)(u >> 11) * (1.0 / 9007199254740992.0);
@@ -559,15 +574,15 @@ struct Dither {
         *sample *= neg_scale;
         switch (type) {
         case 'T': {           // :78-84  r1 - r2, r ~ U[0,0.5]
-            Philox p = philox4x32_10((uint32_t)frame, (uint32_t)(frame >> 32), chan, 0, (uint32_t)seed, (uint32_t)(seed >> 32));
-            double r1 = u53(p.v[0], p.v[1]) * 0.5;
-            double r2 = u53(p.v[2], p.v[3]) * 0.5;
+            Philox2 p = philox2x32_10(frame, chan, seed);
+            double r1 = (double)p.a * (1.0 / 8589934592.0);         // U[0, 0.5) on a 2^-33 grid
+            double r2 = (double)p.b * (1.0 / 8589934592.0);
             *sample += r1 - r2;
             break;
         }
         case 'R': {           // :97-100
-            Philox p = philox4x32_10((uint32_t)frame, (uint32_t)(frame >> 32), chan, 0, (uint32_t)seed, (uint32_t)(seed >> 32));
-            *sample += u53(p.v[0], p.v[1]) - 0.5;
+            Philox2 p = philox2x32_10(frame, chan, seed);
+            *sample += u53(p.a, p.b) - 0.5;
             break;
         }
         case 'F': {           // :102-110
