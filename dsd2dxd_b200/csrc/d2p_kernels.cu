@@ -418,20 +418,24 @@ __device__ __forceinline__ void lutfir_pair(const KParams& P, const LaneLut& L, 
     const uint32_t* pb = tw + (b >> 2);
     const int bsh = (b & 3) * 8;
     uint32_t blA = pb[0], blB = PAIR ? pb[dW] : 0u;
+    // the words of the NEXT group are fetched one group ahead, so that a group never waits on its own tile loads
+    uint32_t nfA = pf[0], nfB = PAIR ? pf[dW] : 0u, nbA = pb[1], nbB = PAIR ? pb[1 + dW] : 0u;
     double accA = 0.0, accB = 0.0;
     uint32_t tp = tp0;
     int i0 = -c;
     const int gp_lo = P.gp_lo, gp_hi = P.gp_hi, ng = P.ngroups;
     int g = 0;
 #define D2P_FETCH()                                                                \
-        const uint32_t flA = pf[0], flB = PAIR ? pf[dW] : 0u;                      \
+        const uint32_t flA = nfA, flB = nfB, bhA = nbA, bhB = nbB;                 \
+        --pf; ++pb;                                                                \
+        nfA = pf[0]; nbA = pb[1];                                                  \
+        if (PAIR) { nfB = pf[dW]; nbB = pb[1 + dW]; }                              \
         const uint32_t qfA = __funnelshift_r(flA, fhA, fsh);                       \
         const uint32_t qfB = PAIR ? __funnelshift_r(flB, fhB, fsh) : 0u;           \
-        fhA = flA; fhB = flB; --pf;                                                \
-        const uint32_t bhA = pb[1], bhB = PAIR ? pb[1 + dW] : 0u;                  \
+        fhA = flA; fhB = flB;                                                      \
         const uint32_t qbA = __brev(__funnelshift_r(blA, bhA, bsh));               \
         const uint32_t qbB = PAIR ? __brev(__funnelshift_r(blB, bhB, bsh)) : 0u;   \
-        blA = bhA; blB = bhB; ++pb;
+        blA = bhA; blB = bhB;
 #define D2P_STEP(GUARD, D)                                                         \
     {                                                                              \
         uint32_t rsel = ((D) & 1) ? L.rlo : L.rhi;                                 \
