@@ -92,16 +92,37 @@ static void lutfir_geometry(const Plan& p, const LutLayout& L, int TF, int* tile
     *smem = (size_t)lutfir_zpad(p.nt, L.K) + (size_t)L.slots * 2048 + 2 * (size_t)*in_buf + 2 * (size_t)*ostage;
 }
 
-static void lm_geometry(const Plan& p, int TF, int* tile_stride, int* s1_cap, int* s2_cap, size_t* smem) {
+// L/M tile geometry (see lm_kernel): NB channel slots of phase-major stage-1 / stage-2 tiles.
+struct LmGeom { int tile_stride, s1_cap, s2_cap, pitch2, pitch3; size_t smem; };
+struct LmLut { int A, Gp, cyc, slots; };       // active lanes per half-warp, block pitch, phase patterns, row slots
+
+static LmLut lm_lut_layout(const Plan& p) {
+    LmLut l;
+    const int L = (int)p.L;
+    l.A = L <= 16 ? L * (16 / L) : 10;          // L = 5 -> 15 lanes, 10 -> 10, 20 -> 10 (two alternating phase patterns)
+    l.cyc = (p.m1 * l.A) % L == 0 ? 1 : 2;
+    l.Gp = p.gmax | 1;
+    l.slots = (l.A * l.cyc * l.Gp + 15) / 16 * 16;
+    return l;
+}
+
+static LmGeom lm_geometry(const Plan& p, const LmLut& ll, int TF, int NB) {
+    LmGeom g;
     const int C = p.cfg.channels;
     const long long k2span = p.nstages == 3 ? (long long)(TF - 1) * p.D3 + (2 * p.h3 - 1) : (TF - 1);
     const long long cnt1 = k2span * p.D2 + (2 * p.h2 - 1) + 1;
-    *s1_cap = (int)((cnt1 + 1) & ~1LL);
-    *s2_cap = p.nstages == 3 ? (int)((k2span + 2) & ~1LL) : 0;
+    g.pitch2 = (int)((cnt1 + p.D2 - 1) / p.D2 + 2) | 1;
+    g.s1_cap = (p.D2 * g.pitch2 + 1) & ~1;
+    g.pitch3 = 0; g.s2_cap = 0;
+    if (p.nstages == 3) {
+        g.pitch3 = (int)((k2span + 1 + p.D3 - 1) / p.D3 + 2) | 1;
+        g.s2_cap = (p.D3 * g.pitch3 + 1) & ~1;
+    }
     const long long bits = cnt1 * p.m1 / p.L + 64 + p.m1;
-    *tile_stride = (int)round16((size_t)(bits / 8) + 16) + 48;
+    g.tile_stride = (int)round16((size_t)(bits / 8) + 16) + 48;
     const size_t ostage = p.cfg.out_format == D2P_OUT_PLANAR_32 ? 0 : round16((size_t)TF * C * p.bps);
-    *smem = (size_t)p.L * p.gmax * 2048 + (size_t)(*s1_cap + *s2_cap) * 8 + (size_t)C * *tile_stride + ostage;
+    g.smem = (size_t)ll.slots * 2048 + (size_t)NB * (g.s1_cap + g.s2_cap) * 8 + (size_t)C * g.tile_stride + ostage;
+    return g;
 }
 
 static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
@@ -151,23 +172,60 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
 
     const size_t budget = (size_t)kMaxSmem - 1024;
     if (dp->lm) {
-        // tile geometry: the largest tile that leaves room for two CTAs per SM if the LUT allows, else one
-        int best_tf = 0;
-        for (int pass = 0; pass < 2 && !best_tf; ++pass) {
-            const size_t lim = pass == 0 ? budget / 2 : budget;
-            for (int tf = 512; tf >= 64; tf >>= 1) {
-                int ts, a = 0, b = 0; size_t sm;
-                lm_geometry(p, tf, &ts, &a, &b, &sm);
-                if (sm <= lim && (pass == 1 || tf >= 128)) { best_tf = tf; break; }
+        if (p.gmax > 5 || p.ring_cap != 32 || (int)p.L > kMaxPhasesDev)
+            return set_err(D2P_ERR_INVALID_ARG, "internal: stage-1 filter outside the kernel's group / ring assumptions");
+        const LmLut ll = lm_lut_layout(p);
+        const int nhw = kMaxThreads / 16;
+        { int a = p.m1 % (int)p.L, b = (int)p.L; while (b) { const int t = a % b; a = b; b = t; }
+          if (a != 1) return set_err(D2P_ERR_INVALID_ARG, "internal: m1 and L are not coprime"); }
+        if (((long long)p.m1 * ll.A * nhw) % p.L != 0 || (ll.cyc == 2 && ((long long)p.m1 * ll.A * 2) % p.L != 0))
+            return set_err(D2P_ERR_INVALID_ARG, "internal: stage-1 phase pattern does not close");
+        // tile geometry: keep the whole CTA busy in stages 2/3 (NB * TF >= threads) with the largest tile that fits
+        int best_tf = 0, best_nb = 0; double best_score = 0.0;
+        const int C = cfg.channels;
+        const double halo = p.nstages == 3 ? (2.0 * p.h3 / p.D3 + 2.0 * p.h2 / (p.D2 * p.D3)) : 2.0 * p.h2 / p.D2;
+        for (int tf = 1024; tf >= 32; tf >>= 1)
+            for (int nb = 1; nb <= C; ++nb) {
+                if (C % nb != 0 && nb != C) continue;
+                const LmGeom g = lm_geometry(p, ll, tf, nb);
+                if (g.smem > budget) continue;
+                const double busy = std::min(1.0, (double)nb * tf / kMaxThreads);
+                const double score = busy * tf / (tf + halo);
+                if (score > best_score * 1.0001) { best_score = score; best_tf = tf; best_nb = nb; }
+            }
+        if (!best_tf) return set_err(D2P_ERR_NOMEM, "filter LUT and tiles do not fit in shared memory");
+        const LmGeom g = lm_geometry(p, ll, best_tf, best_nb);
+        k.TF = best_tf; k.NB = best_nb;
+        k.tile_stride = g.tile_stride; k.s1_cap = g.s1_cap; k.s2_cap = g.s2_cap; k.pitch2 = g.pitch2; k.pitch3 = g.pitch3;
+        dp->smem = g.smem;
+        k.lmA = ll.A; k.lmGp = ll.Gp; k.lm_cyc = ll.cyc; k.lut_row_bytes = ll.slots * 8;
+        k.lm_base_hi = p.stage1_nhi(0);
+        k.lm_step_t = (long long)p.m1 * ll.A * nhw / p.L;
+        const int T2 = 2 * p.h2 - 1;
+        for (int i = 0; i < p.h2; ++i) {
+            k.off2f[i] = (unsigned short)(((T2 - i) % p.D2) * g.pitch2 + (T2 - i) / p.D2);
+            k.off2b[i] = (unsigned short)((i % p.D2) * g.pitch2 + i / p.D2);
+        }
+        if (p.nstages == 3) {
+            const int T3 = 2 * p.h3 - 1;
+            for (int i = 0; i < p.h3; ++i) {
+                k.off3f[i] = (unsigned short)(((T3 - i) % p.D3) * g.pitch3 + (T3 - i) / p.D3);
+                k.off3b[i] = (unsigned short)((i % p.D3) * g.pitch3 + i / p.D3);
             }
         }
-        if (!best_tf) return set_err(D2P_ERR_NOMEM, "filter LUT and tiles do not fit in shared memory");
-        k.TF = best_tf;
-        lm_geometry(p, best_tf, &k.tile_stride, &k.s1_cap, &k.s2_cap, &dp->smem);
-        CK(cudaMalloc(&dp->d_lut, lut.size() * sizeof(double)));
-        CK(cudaMemcpy(dp->d_lut, lut.data(), lut.size() * sizeof(double), cudaMemcpyHostToDevice));
+        // row per byte value; block (u + A*cyc) holds the tables of phase (m1 * (A*cyc + u)) mod L
+        std::vector<double> sk((size_t)256 * ll.slots, 0.0);
+        for (int b = 0; b < 256; ++b)
+            for (int cy = 0; cy < ll.cyc; ++cy)
+                for (int u = 0; u < ll.A; ++u) {
+                    const int ph = (int)(((long long)p.m1 * (ll.A * cy + u)) % p.L);
+                    for (int gq = 0; gq < p.gmax; ++gq)
+                        sk[(size_t)b * ll.slots + (size_t)ll.Gp * (u + ll.A * cy) + gq] = lut[((size_t)ph * p.gmax + gq) * 256 + b];
+                }
+        CK(cudaMalloc(&dp->d_lut, sk.size() * sizeof(double)));
+        CK(cudaMemcpy(dp->d_lut, sk.data(), sk.size() * sizeof(double), cudaMemcpyHostToDevice));
         k.lut = dp->d_lut;
-        k.lut_doubles = (int)lut.size();
+        k.lut_doubles = (int)sk.size();
     } else {
         // integer path: pick the replication (skew depth K) and the tile size together.  More replicas mean
         // fewer idle skew steps per frame (nt / (nt + K - 1)) but a larger LUT; one persistent CTA per SM.

@@ -72,7 +72,12 @@ struct KParams {
     int nstages, L, m1, accum, h1, gmax, ring_mask;
     long long e0;
     int h2, D2, h3, D3;
-    int s1_cap, s2_cap;       // doubles reserved for the stage-1 / stage-2 tiles
+    int s1_cap, s2_cap;       // doubles per channel slot of the stage-1 / stage-2 tiles
+    int NB;                   // channel slots kept in flight together
+    int pitch2, pitch3;       // doubles per phase row of the phase-major stage-1 / stage-2 tiles
+    int lmA, lmGp, lm_cyc;    // active lanes per half-warp, LUT block pitch (slots, odd), phase patterns (1 or 2)
+    long long lm_base_hi;     // high-rate index of stage-1 output 0
+    long long lm_step_t;      // input-time step of one half-warp iteration: m1 * A * (threads/16) / L
     unsigned char groups[kMaxPhasesDev];
 
     DevStats* stats;
@@ -81,6 +86,11 @@ struct KParams {
 
     double c2[kMaxFirTapsDev];   // first h2 entries of reverse(half2): the taps convolve_direct walks
     double c3[kMaxFir3TapsDev];
+    // phase-major element offsets of the front / back sample of every tap (same for every tile)
+    unsigned short off2f[kMaxFirTapsDev], off2b[kMaxFirTapsDev];
+    unsigned short off3f[kMaxFir3TapsDev], off3b[kMaxFir3TapsDev];
 };
+
+static_assert(sizeof(KParams) <= 4096, "kernel parameter block is limited to 4 KB");
 
 }  // namespace d2p

@@ -584,17 +584,32 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
 
 // ------------------------------------------------------------------------------------------------
 // Rational L/M path.
-//   stage 1: output n sits at high-rate index n_hi (Plan::stage1_nhi); t = n_hi div L, p = n_hi mod L
+//   stage 1: output n sits at high-rate index n_hi = base_hi + m1*n; t = n_hi div L, p = n_hi mod L
 //            y1[n] = fold_g LUT[p][g][ window8(t - (8g mod ring_cap)) ],  window8(t) bit j = x[t-j]
 //            (pre-stream bits read 0; the modulo reproduces the reference's 32-entry byte ring)
 //   stage s: y_s[k] = fold_{j<h} total + F[j]*(y[t-j] + y[t-(2h-1-j)]),  t = (h-1) + k*D, pre-stream = 0.0
+//
+// Both stages are bound by the shared-memory crossbar, so the layouts are chosen to make every warp-wide
+// 8-byte access conflict-free (profiles/r01_lm_v1_*: 56 % of the wavefronts of the first version were
+// bank-conflict replays):
+//   * stage-1 LUT: one row per byte value; inside a row, lane u (of the A active lanes of a half-warp) owns the
+//     block of slots [Gp*u, Gp*u + G) holding the G tables of ITS phase.  Gp is odd, so the 16 blocks start in
+//     16 different bank pairs.  Half-warps take A = L*floor(16/L) consecutive outputs starting at an output of
+//     phase 0, hence lane u always has phase (m1*u) mod L: no per-output division, no phase look-up;
+//   * stage-1 results are stored phase-major with respect to the stage-2 decimation: sample n of the tile goes
+//     to s1[(n mod D2)*pitch + n div D2].  Output j of stage 2 reads, at tap k, row (T0-k) mod D2 at column
+//     (T0-k) div D2 + j: lanes = consecutive outputs read consecutive doubles.  The per-tap (row, column)
+//     offsets are the same for every tile and come from the parameter block (off2f/off2b);
+//   * stage 3 (when present) reads stage-2 results laid out the same way with respect to D3.
+// NB channels are kept in flight together so that stages 2/3, which have only TF-ish outputs per channel,
+// still occupy the whole CTA.
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ double fir_sym(const double* __restrict__ taps, const double* __restrict__ front,
-                                          const double* __restrict__ back, int h) {
+__device__ __forceinline__ double fir_sym_t(const double* __restrict__ taps, const unsigned short* __restrict__ offf,
+                                            const unsigned short* __restrict__ offb, const double* __restrict__ col, int h) {
     double total = 0.0;
 #pragma unroll 4
     for (int k = 0; k < h; ++k)
-        total = __dadd_rn(total, __dmul_rn(taps[k], __dadd_rn(front[-k], back[k])));
+        total = __dadd_rn(total, __dmul_rn(taps[k], __dadd_rn(col[offf[k]], col[offb[k]])));
     return total;
 }
 
@@ -602,14 +617,24 @@ __global__ void __launch_bounds__(kMaxThreads) lm_kernel(const __grid_constant__
     extern __shared__ __align__(16) unsigned char smem[];
     double* lut = reinterpret_cast<double*>(smem);
     double* s1 = lut + P.lut_doubles;
-    double* s2 = s1 + P.s1_cap;
-    unsigned char* tiles = reinterpret_cast<unsigned char*>(s2 + P.s2_cap);
+    double* s2 = s1 + (size_t)P.NB * P.s1_cap;
+    unsigned char* tiles = reinterpret_cast<unsigned char*>(s2 + (size_t)P.NB * P.s2_cap);
     unsigned char* ostage = tiles + (size_t)P.C * P.tile_stride;
 
-    __shared__ unsigned char sgroups[kMaxPhasesDev];
-    if (threadIdx.x < kMaxPhasesDev) sgroups[threadIdx.x] = P.groups[threadIdx.x];
     load_lut(lut, P.lut, P.lut_doubles);
     Emitter<0, 0> em; em.init();
+
+    const int tid = threadIdx.x;
+    const int u = tid & 15, hw = tid >> 4, nhw = blockDim.x >> 4;
+    const int A = P.lmA;
+    // block of this lane: u, or u + A for odd half-warps when the phase pattern alternates (lm_cyc == 2)
+    const uint32_t tpl = (uint32_t)__cvta_generic_to_shared(lut) + (uint32_t)(P.lmGp * (u + A * (hw & (P.lm_cyc - 1))) * 8);
+    const uint32_t rlo = (uint32_t)P.lut_row_bytes, rhi = (uint32_t)P.lut_row_bytes << 16;
+    const int gmax = P.gmax;
+    // one half-warp iteration advances A*nhw outputs: (row, column) step of the phase-major store
+    const int step_n = A * nhw;
+    const int step_q = step_n / P.D2, step_ph = step_n - step_q * P.D2;
+    const long long step_t = P.lm_step_t;                           // = m1 * A * nhw / L (exact)
 
     for (unsigned int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x) {
         const DevJob& J = find_job(P, tile);
@@ -626,71 +651,100 @@ __global__ void __launch_bounds__(kMaxThreads) lm_kernel(const __grid_constant__
         // stage-1 output range feeding those
         const long long n_lo = (P.h2 - 1) + k2c * P.D2 - (2 * P.h2 - 1);
         const long long n_hi = (P.h2 - 1) + k2_hi * P.D2;
-        const int cnt1 = (int)(n_hi - n_lo + 1);
         const int cnt2 = (int)(k2_hi - k2_lo + 1);
-        const long long nc = n_lo > 0 ? n_lo : 0;
+        const long long ncl = n_lo > 0 ? n_lo : 0;
         // input bits feeding those
-        const long long nhi_first = P.accum ? (P.e0 + nc + 1) * 21 - 1 : (long long)(P.h1 - 1) + (long long)P.m1 * (nc + 1);
-        const long long nhi_last = P.accum ? (P.e0 + n_hi + 1) * 21 - 1 : (long long)(P.h1 - 1) + (long long)P.m1 * (n_hi + 1);
+        const long long nhi_first = P.lm_base_hi + (long long)P.m1 * ncl;
+        const long long nhi_last = P.lm_base_hi + (long long)P.m1 * n_hi;
         const long long t_first = nhi_first / P.L;
-        const int p_first = (int)(nhi_first - t_first * P.L);
         const long long t_last = nhi_last / P.L;
-        long long byte_lo = (t_first - 31) >> 3;                    // arithmetic shift: floor for negatives
+        const long long byte_lo = (t_first - 31) >> 3;              // arithmetic shift: floor for negatives
         const long long s_lo = byte_lo & ~15LL;
         const int nbytes = (int)((((t_last >> 3) + 1 - s_lo) + 15) & ~15LL) + 16;
-        const int bit_base = (int)(t_first - 31 - 8 * s_lo);        // tile-relative bit of the first window's oldest bit
+
+        // first output of phase 0 at or before n_lo: half-warps start there, lane u then has phase (m1*u) mod L
+        int ph0;
+        {
+            const long long num = P.lm_base_hi + (long long)P.m1 * n_lo;
+            long long tq = num >= 0 ? num / P.L : -((-num + P.L - 1) / P.L);
+            ph0 = (int)(num - tq * P.L);
+        }
+        int back = 0;
+        while (ph0 != 0) { ph0 -= P.m1 % P.L; if (ph0 < 0) ph0 += P.L; ++back; }
+        const long long nA = n_lo - back;
+        // this thread's first output, its window time and its place in the phase-major buffer
+        const long long n_first = nA + (long long)A * hw + u;
+        long long t_thr;
+        {
+            const long long num = P.lm_base_hi + (long long)P.m1 * n_first;
+            t_thr = num >= 0 ? num / P.L : -((-num + P.L - 1) / P.L);
+        }
+        int rel0 = (int)(n_first - n_lo);                           // >= -back > -L
+        if (rel0 < 0) { rel0 += step_n; t_thr += step_t; }          // outputs before the tile's first one are not needed
+        const int q0 = rel0 / P.D2, p0 = rel0 - q0 * P.D2;
+        const int last_rel = (int)(n_hi - n_lo);
 
         __syncthreads();
-        stage_input(P, J, tiles, s_lo, nbytes, threadIdx.x, blockDim.x);
+        stage_input(P, J, tiles, s_lo, nbytes, tid, blockDim.x);
         __syncthreads();
 
-        for (int c = 0; c < P.C; ++c) {
-            const uint32_t* tw = reinterpret_cast<const uint32_t*>(tiles + (size_t)c * P.tile_stride);
-            // ---- stage 1 ----
-            for (int idx = threadIdx.x; idx < cnt1; idx += blockDim.x) {
-                const long long n = n_lo + idx;
-                double y = 0.0;                                     // pre-stream stage-1 samples are 0.0 (ring zero-init)
-                if (n >= 0) {
-                    const unsigned int x = (unsigned int)p_first + (unsigned int)P.m1 * (unsigned int)(n - nc);
-                    const unsigned int dt = x / (unsigned int)P.L;
-                    const int p = (int)(x - dt * (unsigned int)P.L);
-                    const int d = bit_base + (int)dt;
-                    const int w = d >> 5;
-                    const uint32_t z = __brev(__funnelshift_r(tw[w], tw[w + 1], d & 31));   // bit j = x[t-j]
-                    const double* T = lut + (size_t)p * P.gmax * 256;
-                    const int G = sgroups[p];
-                    y = T[z & 0xFF];
-                    for (int g = 1; g < G; ++g)
-                        y = __dadd_rn(y, T[g * 256 + ((z >> ((8 * g) & P.ring_mask)) & 0xFF)]);
+        for (int cb = 0; cb < P.C; cb += P.NB) {
+            const int nbc = P.C - cb < P.NB ? P.C - cb : P.NB;
+            // ---- stage 1 (A1 + A7/A8) ----
+            if (u < A) {
+                for (int sl = 0; sl < nbc; ++sl) {
+                    const uint32_t* tw = reinterpret_cast<const uint32_t*>(tiles + (size_t)(cb + sl) * P.tile_stride);
+                    double* dst = s1 + (size_t)sl * P.s1_cap;
+                    long long t = t_thr;
+                    int rel = rel0, q = q0, ph = p0;
+                    for (; rel <= last_rel; rel += step_n, t += step_t) {
+                        {
+                            double y = 0.0;                         // pre-stream stage-1 samples are 0.0 (ring zero-init)
+                            if (n_lo + rel >= 0) {
+                                const int d = (int)(t - 31 - 8 * s_lo);   // tile-relative bit of the window's oldest bit
+                                const int w = d >> 5;
+                                const uint32_t z = __brev(__funnelshift_r(tw[w], tw[w + 1], d & 31));   // bit j = x[t-j]
+                                y = lds_f64<0>(__dp2a_lo(rlo, z, tpl));
+                                if (gmax > 1) y = __dadd_rn(y, lds_f64<8>(__dp2a_lo(rhi, z, tpl)));
+                                if (gmax > 2) y = __dadd_rn(y, lds_f64<16>(__dp2a_hi(rlo, z, tpl)));
+                                if (gmax > 3) y = __dadd_rn(y, lds_f64<24>(__dp2a_hi(rhi, z, tpl)));
+                                if (gmax > 4) y = __dadd_rn(y, lds_f64<32>(__dp2a_lo(rlo, z, tpl)));   // 8g mod 32: byte 0 again
+                            }
+                            dst[ph * P.pitch2 + q] = y;
+                        }
+                        q += step_q; ph += step_ph;
+                        if (ph >= P.D2) { ph -= P.D2; ++q; }
+                    }
                 }
-                s1[idx] = y;
             }
             __syncthreads();
-            // ---- stage 2 ----
-            for (int idx = threadIdx.x; idx < cnt2; idx += blockDim.x) {
+            // ---- stage 2 (A9) ----
+            for (int item = tid; item < nbc * cnt2; item += blockDim.x) {
+                const int sl = item / cnt2, idx = item - sl * cnt2;
                 const long long k2 = k2_lo + idx;
                 double tot = 0.0;
-                if (k2 >= 0) {
-                    const int rel = (int)((P.h2 - 1) + k2 * P.D2 - n_lo);
-                    tot = fir_sym(P.c2, s1 + rel, s1 + rel - (2 * P.h2 - 1), P.h2);
+                if (k2 >= 0)
+                    tot = fir_sym_t(P.c2, P.off2f, P.off2b, s1 + (size_t)sl * P.s1_cap + (int)(k2 - k2c), P.h2);
+                if (P.nstages == 2) em.emit(P, J, ostage, cb + sl, f0 + idx, idx, tot);
+                else {
+                    const int qq = idx / P.D3;
+                    s2[(size_t)sl * P.s2_cap + (idx - qq * P.D3) * P.pitch3 + qq] = tot;
                 }
-                if (P.nstages == 2) em.emit(P, J, ostage, c, f0 + idx, idx, tot);
-                else s2[idx] = tot;
             }
             // ---- stage 3 ----
             if (P.nstages == 3) {
                 __syncthreads();
-                for (int idx = threadIdx.x; idx < nf; idx += blockDim.x) {
-                    const int rel = (int)((P.h3 - 1) + (f0 + idx) * P.D3 - k2_lo);
-                    const double y = fir_sym(P.c3, s2 + rel, s2 + rel - (2 * P.h3 - 1), P.h3);
-                    em.emit(P, J, ostage, c, f0 + idx, idx, y);
+                for (int item = tid; item < nbc * nf; item += blockDim.x) {
+                    const int sl = item / nf, idx = item - sl * nf;
+                    const double y = fir_sym_t(P.c3, P.off3f, P.off3b, s2 + (size_t)sl * P.s2_cap + idx, P.h3);
+                    em.emit(P, J, ostage, cb + sl, f0 + idx, idx, y);
                 }
             }
-            __syncthreads();                                        // s1/s2 are reused by the next channel
+            __syncthreads();                                        // s1/s2 are reused by the next channel group
         }
         if (P.out_format != D2P_DEV_OUT_PLANAR) {
             const size_t fb = (size_t)P.C * P.bps;
-            copy_out(J.out + (size_t)(f0 - J.f_begin) * fb, ostage, (int)(nf * fb), threadIdx.x, blockDim.x);
+            copy_out(J.out + (size_t)(f0 - J.f_begin) * fb, ostage, (int)(nf * fb), tid, blockDim.x);
         }
     }
     em.flush(P);
