@@ -93,7 +93,7 @@ static void lutfir_geometry(const Plan& p, const LutLayout& L, int TF, int* tile
 }
 
 // L/M tile geometry (see lm_kernel): NB channel slots of phase-major stage-1 / stage-2 tiles.
-struct LmGeom { int tile_stride, s1_cap, s2_cap, pitch2, pitch3; size_t smem; };
+struct LmGeom { int tile_stride, s1_cap, s2_cap, pitch2, pitch3, ostage; size_t smem; };
 struct LmLut { int A, Gp, cyc, slots; };       // active lanes per half-warp, block pitch, phase patterns, row slots
 
 static LmLut lm_lut_layout(const Plan& p) {
@@ -111,17 +111,18 @@ static LmGeom lm_geometry(const Plan& p, const LmLut& ll, int TF, int NB) {
     const int C = p.cfg.channels;
     const long long k2span = p.nstages == 3 ? (long long)(TF - 1) * p.D3 + (2 * p.h3 - 1) : (TF - 1);
     const long long cnt1 = k2span * p.D2 + (2 * p.h2 - 1) + 1;
-    g.pitch2 = (int)((cnt1 + p.D2 - 1) / p.D2 + 2) | 1;
+    g.pitch2 = (int)((cnt1 + 2 * p.D2 - 1) / p.D2 + 2) | 1;     // + one column for the sigma shift
     g.s1_cap = (p.D2 * g.pitch2 + 1) & ~1;
     g.pitch3 = 0; g.s2_cap = 0;
     if (p.nstages == 3) {
-        g.pitch3 = (int)((k2span + 1 + p.D3 - 1) / p.D3 + 2) | 1;
+        g.pitch3 = (int)((k2span + 1 + 2 * p.D3 - 1) / p.D3 + 2) | 1;
         g.s2_cap = (p.D3 * g.pitch3 + 1) & ~1;
     }
     const long long bits = cnt1 * p.m1 / p.L + 64 + p.m1;
     g.tile_stride = (int)round16((size_t)(bits / 8) + 16) + 48;
     const size_t ostage = p.cfg.out_format == D2P_OUT_PLANAR_32 ? 0 : round16((size_t)TF * C * p.bps);
-    g.smem = (size_t)ll.slots * 2048 + (size_t)NB * (g.s1_cap + g.s2_cap) * 8 + (size_t)C * g.tile_stride + ostage;
+    g.ostage = (int)ostage;
+    g.smem = (size_t)ll.slots * 2048 + (size_t)NB * (g.s1_cap + g.s2_cap) * 8 + 2 * (size_t)C * g.tile_stride + 2 * ostage;
     return g;
 }
 
@@ -175,7 +176,7 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
         if (p.gmax > 5 || p.ring_cap != 32 || (int)p.L > kMaxPhasesDev)
             return set_err(D2P_ERR_INVALID_ARG, "internal: stage-1 filter outside the kernel's group / ring assumptions");
         const LmLut ll = lm_lut_layout(p);
-        const int nhw = kMaxThreads / 16;
+        const int nhw = kLmConsumers / 16;
         { int a = p.m1 % (int)p.L, b = (int)p.L; while (b) { const int t = a % b; a = b; b = t; }
           if (a != 1) return set_err(D2P_ERR_INVALID_ARG, "internal: m1 and L are not coprime"); }
         if (((long long)p.m1 * ll.A * nhw) % p.L != 0 || (ll.cyc == 2 && ((long long)p.m1 * ll.A * 2) % p.L != 0))
@@ -184,12 +185,12 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
         int best_tf = 0, best_nb = 0; double best_score = 0.0;
         const int C = cfg.channels;
         const double halo = p.nstages == 3 ? (2.0 * p.h3 / p.D3 + 2.0 * p.h2 / (p.D2 * p.D3)) : 2.0 * p.h2 / p.D2;
-        for (int tf = 1024; tf >= 32; tf >>= 1)
+        for (int tf = 1024; tf >= 32; tf -= 32)
             for (int nb = 1; nb <= C; ++nb) {
                 if (C % nb != 0 && nb != C) continue;
                 const LmGeom g = lm_geometry(p, ll, tf, nb);
                 if (g.smem > budget) continue;
-                const double busy = std::min(1.0, (double)nb * tf / kMaxThreads);
+                const double busy = std::min(1.0, (double)nb * tf / 512.0);   // stages 2/3: >= 16 warps of outputs
                 const double score = busy * tf / (tf + halo);
                 if (score > best_score * 1.0001) { best_score = score; best_tf = tf; best_nb = nb; }
             }
@@ -201,18 +202,12 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
         k.lmA = ll.A; k.lmGp = ll.Gp; k.lm_cyc = ll.cyc; k.lut_row_bytes = ll.slots * 8;
         k.lm_base_hi = p.stage1_nhi(0);
         k.lm_step_t = (long long)p.m1 * ll.A * nhw / p.L;
-        const int T2 = 2 * p.h2 - 1;
-        for (int i = 0; i < p.h2; ++i) {
-            k.off2f[i] = (unsigned short)(((T2 - i) % p.D2) * g.pitch2 + (T2 - i) / p.D2);
-            k.off2b[i] = (unsigned short)((i % p.D2) * g.pitch2 + i / p.D2);
-        }
-        if (p.nstages == 3) {
-            const int T3 = 2 * p.h3 - 1;
-            for (int i = 0; i < p.h3; ++i) {
-                k.off3f[i] = (unsigned short)(((T3 - i) % p.D3) * g.pitch3 + (T3 - i) / p.D3);
-                k.off3b[i] = (unsigned short)((i % p.D3) * g.pitch3 + i / p.D3);
-            }
-        }
+        k.ostage_bytes = g.ostage;
+        dp->threads = kLmThreads;
+        k.sigma2 = (p.D2 - p.h2 % p.D2) % p.D2;
+        k.sigma3 = p.nstages == 3 ? (p.D3 - p.h3 % p.D3) % p.D3 : 0;
+        k.inv_d2 = (65536 + p.D2 - 1) / p.D2;
+        k.inv_d3 = p.nstages == 3 ? (65536 + p.D3 - 1) / p.D3 : 0;
         // row per byte value; block (u + A*cyc) holds the tables of phase (m1 * (A*cyc + u)) mod L
         std::vector<double> sk((size_t)256 * ll.slots, 0.0);
         for (int b = 0; b < 256; ++b)

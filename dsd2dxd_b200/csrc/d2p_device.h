@@ -72,6 +72,8 @@ struct KParams {
     int nstages, L, m1, accum, h1, gmax, ring_mask;
     long long e0;
     int h2, D2, h3, D3;
+    int sigma2, sigma3;       // element shift of the phase-major tiles: -h (mod D), aligns the FIR walkers' wraps
+    int inv_d2, inv_d3;       // ceil(65536 / D): (x * inv) >> 16 == x / D for the small x the kernels divide
     int s1_cap, s2_cap;       // doubles per channel slot of the stage-1 / stage-2 tiles
     int NB;                   // channel slots kept in flight together
     int pitch2, pitch3;       // doubles per phase row of the phase-major stage-1 / stage-2 tiles
@@ -86,9 +88,6 @@ struct KParams {
 
     double c2[kMaxFirTapsDev];   // first h2 entries of reverse(half2): the taps convolve_direct walks
     double c3[kMaxFir3TapsDev];
-    // phase-major element offsets of the front / back sample of every tap (same for every tile)
-    unsigned short off2f[kMaxFirTapsDev], off2b[kMaxFirTapsDev];
-    unsigned short off3f[kMaxFir3TapsDev], off3b[kMaxFir3TapsDev];
 };
 
 static_assert(sizeof(KParams) <= 4096, "kernel parameter block is limited to 4 KB");

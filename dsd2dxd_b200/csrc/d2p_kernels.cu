@@ -604,150 +604,214 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
 // NB channels are kept in flight together so that stages 2/3, which have only TF-ish outputs per channel,
 // still occupy the whole CTA.
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ double fir_sym_t(const double* __restrict__ taps, const unsigned short* __restrict__ offf,
-                                            const unsigned short* __restrict__ offb, const double* __restrict__ col, int h) {
+// Direct symmetric FIR over a phase-major tile (DecimFIRSym::convolve_direct, rd/lm_resampler.rs:717-751).
+// Sample e of the tile lives at row (e + sigma) mod D, column (e + sigma) div D.  Tap k reads the front sample
+// e = T0 - k and the back sample e = k: the front address walks one row down per tap, the back address one row
+// up.  sigma = -h (mod D) makes both walkers wrap at the same taps (rows rf and D-1-rf), so the taps split into
+// a few straight runs.  `col` already points at this output's column.  All bookkeeping is warp-uniform.
+__device__ __forceinline__ double fir_sym_t(const double* __restrict__ taps, const double* __restrict__ col, int h, int D,
+                                            int pitch, int sigma) {
+    const int ef = 2 * h - 1 + sigma;                               // front element of tap 0 (T0 = 2h-1), shifted
+    int rf = ef % D;
+    const double* pf = col + rf * pitch + ef / D;
+    const double* pb = col + sigma * pitch;                         // back element of tap 0: row sigma == D-1-rf, column 0
+    const int wrap = D * pitch - 1;
     double total = 0.0;
+    int k = 0;
+    while (k < h) {
+        int run = rf + 1;                                           // taps until both walkers leave the tile rows
+        if (h - k < run) run = h - k;
 #pragma unroll 4
-    for (int k = 0; k < h; ++k)
-        total = __dadd_rn(total, __dmul_rn(taps[k], __dadd_rn(col[offf[k]], col[offb[k]])));
+        for (int i = 0; i < run; ++i) {
+            total = __dadd_rn(total, __dmul_rn(taps[k + i], __dadd_rn(*pf, *pb)));
+            pf -= pitch; pb += pitch;
+        }
+        k += run;
+        rf = D - 1; pf += wrap; pb -= wrap;                         // front: previous column, top row; back: next column, row 0
+    }
     return total;
 }
 
-__global__ void __launch_bounds__(kMaxThreads) lm_kernel(const __grid_constant__ KParams P) {
+struct LmTile {                 // per-tile header, computed by one thread
+    const DevJob* J;
+    long long f0, k2_lo, s_lo;
+    int nf, cnt2, j2_0, last_rel, relz, back, dA, nbytes;
+};
+
+__device__ __forceinline__ void lm_tile_header(const KParams& P, unsigned int tile, LmTile& H) {
+    const DevJob& J = find_job(P, tile);
+    H.J = &J;
+    const long long f0 = J.f_begin + (long long)(tile - J.tile_begin) * P.TF;
+    const long long left = J.f_begin + J.f_count - f0;
+    const int nf = left < P.TF ? (int)left : P.TF;
+    H.f0 = f0; H.nf = nf;
+    // stage-2 output range feeding the tile (for 2 stages it *is* the tile)
+    long long k2_lo, k2_hi;
+    if (P.nstages == 3) { k2_lo = (P.h3 - 1) + f0 * P.D3 - (2 * P.h3 - 1); k2_hi = (P.h3 - 1) + (f0 + nf - 1) * P.D3; }
+    else { k2_lo = f0; k2_hi = f0 + nf - 1; }
+    const long long k2c = k2_lo > 0 ? k2_lo : 0;
+    H.k2_lo = k2_lo; H.cnt2 = (int)(k2_hi - k2_lo + 1); H.j2_0 = (int)(k2_lo - k2c);   // <= 0: column of stage-2 output idx is idx + j2_0
+    // stage-1 output range feeding those
+    const long long n_lo = (P.h2 - 1) + k2c * P.D2 - (2 * P.h2 - 1);
+    const long long n_hi = (P.h2 - 1) + k2_hi * P.D2;
+    H.last_rel = (int)(n_hi - n_lo);
+    H.relz = n_lo < 0 ? (int)(-n_lo) : 0;                          // first tile-relative output that exists (n >= 0)
+    // input bits feeding those
+    const long long ncl = n_lo > 0 ? n_lo : 0;
+    const long long t_first = (P.lm_base_hi + (long long)P.m1 * ncl) / P.L;
+    const long long t_last = (P.lm_base_hi + (long long)P.m1 * n_hi) / P.L;
+    const long long s_lo = ((t_first - 31) >> 3) & ~15LL;          // arithmetic shift: floor for negatives
+    H.s_lo = s_lo;
+    H.nbytes = (int)((((t_last >> 3) + 1 - s_lo) + 15) & ~15LL) + 16;
+    // first output of phase 0 at or before n_lo: half-warps start there, lane u then has phase (m1*u) mod L
+    const long long num = P.lm_base_hi + (long long)P.m1 * n_lo;
+    long long tq = num >= 0 ? num / P.L : -((-num + P.L - 1) / P.L);
+    int ph = (int)(num - tq * P.L), back = 0;
+    const int dm = P.m1 % P.L;
+    while (ph != 0) { ph -= dm; if (ph < 0) ph += P.L; ++back; }
+    H.back = back;
+    const long long numA = num - (long long)P.m1 * back;           // multiple of L
+    const long long tA = numA >= 0 ? numA / P.L : -((-numA) / P.L);
+    H.dA = (int)(tA - 31 - 8 * s_lo);                              // tile-relative bit of output nA's oldest window bit
+}
+
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" :: "n"(kLmConsumers) : "memory"); }
+
+// kLmConsumers consumer threads run the stages; kLmProducers extra threads stage the next tile's input from
+// HBM and copy the previous tile's packed PCM out (double-buffered), so no consumer ever waits on HBM.
+template <int GMAX>
+__global__ void __launch_bounds__(kLmThreads) lm_kernel(const __grid_constant__ KParams P) {
     extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ LmTile hdr[2];
     double* lut = reinterpret_cast<double*>(smem);
     double* s1 = lut + P.lut_doubles;
     double* s2 = s1 + (size_t)P.NB * P.s1_cap;
-    unsigned char* tiles = reinterpret_cast<unsigned char*>(s2 + (size_t)P.NB * P.s2_cap);
-    unsigned char* ostage = tiles + (size_t)P.C * P.tile_stride;
+    unsigned char* tiles0 = reinterpret_cast<unsigned char*>(s2 + (size_t)P.NB * P.s2_cap);
+    const size_t tiles_bytes = (size_t)P.C * P.tile_stride;
+    unsigned char* ostage0 = tiles0 + 2 * tiles_bytes;
+
+    const int tid = threadIdx.x;
+    const bool producer = tid >= kLmConsumers;
+    const int ptid = tid - kLmConsumers, np = blockDim.x - kLmConsumers;
+    const bool staged_out = P.out_format != D2P_DEV_OUT_PLANAR;
+    const size_t fb = (size_t)P.C * P.bps;
 
     load_lut(lut, P.lut, P.lut_doubles);
     Emitter<0, 0> em; em.init();
 
-    const int tid = threadIdx.x;
-    const int u = tid & 15, hw = tid >> 4, nhw = blockDim.x >> 4;
+    const int u = tid & 15, hw = tid >> 4, nhw = kLmConsumers >> 4;
     const int A = P.lmA;
     // block of this lane: u, or u + A for odd half-warps when the phase pattern alternates (lm_cyc == 2)
     const uint32_t tpl = (uint32_t)__cvta_generic_to_shared(lut) + (uint32_t)(P.lmGp * (u + A * (hw & (P.lm_cyc - 1))) * 8);
     const uint32_t rlo = (uint32_t)P.lut_row_bytes, rhi = (uint32_t)P.lut_row_bytes << 16;
-    const int gmax = P.gmax;
     // one half-warp iteration advances A*nhw outputs: (row, column) step of the phase-major store
     const int step_n = A * nhw;
     const int step_q = step_n / P.D2, step_ph = step_n - step_q * P.D2;
-    const long long step_t = P.lm_step_t;                           // = m1 * A * nhw / L (exact)
+    const int step_t = (int)P.lm_step_t;                            // = m1 * A * nhw / L (exact)
+    const int step_el = step_ph * P.pitch2 + step_q, wrap_el = 1 - P.D2 * P.pitch2;
+    const int own = A * hw + u;                                     // this thread's output offset from nA
+    const int own_t = (P.m1 * own) / P.L;                           // ... and its input-time offset (nA has phase 0)
 
-    for (unsigned int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x) {
-        const DevJob& J = find_job(P, tile);
-        em.set_job(J);
-        const long long f0 = J.f_begin + (long long)(tile - J.tile_begin) * P.TF;
-        const long long left = J.f_begin + J.f_count - f0;
-        const int nf = left < P.TF ? (int)left : P.TF;
+    LmTile Hp, Hc;                                                  // producers: previous / current tile
+    Hp.J = nullptr; Hc.J = nullptr;
+    unsigned int tile = blockIdx.x;
+    if (producer && tile < P.total_tiles) {
+        lm_tile_header(P, tile, Hc);
+        if (ptid == 0) hdr[0] = Hc;
+        stage_input(P, *Hc.J, tiles0, Hc.s_lo, Hc.nbytes, ptid, np);
+    }
+    __syncthreads();
 
-        // stage-2 output range feeding the tile (for 2 stages it *is* the tile)
-        long long k2_lo, k2_hi;
-        if (P.nstages == 3) { k2_lo = (P.h3 - 1) + f0 * P.D3 - (2 * P.h3 - 1); k2_hi = (P.h3 - 1) + (f0 + nf - 1) * P.D3; }
-        else { k2_lo = f0; k2_hi = f0 + nf - 1; }
-        const long long k2c = k2_lo > 0 ? k2_lo : 0;
-        // stage-1 output range feeding those
-        const long long n_lo = (P.h2 - 1) + k2c * P.D2 - (2 * P.h2 - 1);
-        const long long n_hi = (P.h2 - 1) + k2_hi * P.D2;
-        const int cnt2 = (int)(k2_hi - k2_lo + 1);
-        const long long ncl = n_lo > 0 ? n_lo : 0;
-        // input bits feeding those
-        const long long nhi_first = P.lm_base_hi + (long long)P.m1 * ncl;
-        const long long nhi_last = P.lm_base_hi + (long long)P.m1 * n_hi;
-        const long long t_first = nhi_first / P.L;
-        const long long t_last = nhi_last / P.L;
-        const long long byte_lo = (t_first - 31) >> 3;              // arithmetic shift: floor for negatives
-        const long long s_lo = byte_lo & ~15LL;
-        const int nbytes = (int)((((t_last >> 3) + 1 - s_lo) + 15) & ~15LL) + 16;
+    for (int j = 0; tile < P.total_tiles; tile += gridDim.x, ++j) {
+        const int bsel = j & 1;
+        if (producer) {
+            const unsigned int nxt = tile + gridDim.x;
+            LmTile Hn; Hn.J = nullptr;
+            if (nxt < P.total_tiles) {
+                lm_tile_header(P, nxt, Hn);
+                if (ptid == 0) hdr[bsel ^ 1] = Hn;
+                stage_input(P, *Hn.J, tiles0 + (size_t)(bsel ^ 1) * tiles_bytes, Hn.s_lo, Hn.nbytes, ptid, np);
+            }
+            if (Hp.J && staged_out)
+                copy_out(Hp.J->out + (size_t)(Hp.f0 - Hp.J->f_begin) * fb, ostage0 + (size_t)(bsel ^ 1) * P.ostage_bytes,
+                         (int)(Hp.nf * fb), ptid, np);
+            Hp = Hc; Hc = Hn;
+        } else {
+            const LmTile& H = hdr[bsel];
+            const DevJob& J = *H.J;
+            const unsigned char* tiles = tiles0 + (size_t)bsel * tiles_bytes;
+            unsigned char* ostage = ostage0 + (size_t)bsel * P.ostage_bytes;
+            em.set_job(J);
+            const long long f0 = H.f0;
+            const int nf = H.nf, cnt2 = H.cnt2, last_rel = H.last_rel, relz = H.relz;
 
-        // first output of phase 0 at or before n_lo: half-warps start there, lane u then has phase (m1*u) mod L
-        int ph0;
-        {
-            const long long num = P.lm_base_hi + (long long)P.m1 * n_lo;
-            long long tq = num >= 0 ? num / P.L : -((-num + P.L - 1) / P.L);
-            ph0 = (int)(num - tq * P.L);
-        }
-        int back = 0;
-        while (ph0 != 0) { ph0 -= P.m1 % P.L; if (ph0 < 0) ph0 += P.L; ++back; }
-        const long long nA = n_lo - back;
-        // this thread's first output, its window time and its place in the phase-major buffer
-        const long long n_first = nA + (long long)A * hw + u;
-        long long t_thr;
-        {
-            const long long num = P.lm_base_hi + (long long)P.m1 * n_first;
-            t_thr = num >= 0 ? num / P.L : -((-num + P.L - 1) / P.L);
-        }
-        int rel0 = (int)(n_first - n_lo);                           // >= -back > -L
-        if (rel0 < 0) { rel0 += step_n; t_thr += step_t; }          // outputs before the tile's first one are not needed
-        const int q0 = rel0 / P.D2, p0 = rel0 - q0 * P.D2;
-        const int last_rel = (int)(n_hi - n_lo);
+            int rel0 = own - H.back, d0 = H.dA + own_t;
+            if (rel0 < 0) { rel0 += step_n; d0 += step_t; }        // outputs before the tile's first one are not needed
+            const int e0 = rel0 + P.sigma2;                         // shifted element index (see fir_sym_t)
+            const int q0 = (e0 * P.inv_d2) >> 16, p0 = e0 - q0 * P.D2;
 
-        __syncthreads();
-        stage_input(P, J, tiles, s_lo, nbytes, tid, blockDim.x);
-        __syncthreads();
-
-        for (int cb = 0; cb < P.C; cb += P.NB) {
-            const int nbc = P.C - cb < P.NB ? P.C - cb : P.NB;
-            // ---- stage 1 (A1 + A7/A8) ----
-            if (u < A) {
-                for (int sl = 0; sl < nbc; ++sl) {
-                    const uint32_t* tw = reinterpret_cast<const uint32_t*>(tiles + (size_t)(cb + sl) * P.tile_stride);
-                    double* dst = s1 + (size_t)sl * P.s1_cap;
-                    long long t = t_thr;
-                    int rel = rel0, q = q0, ph = p0;
-                    for (; rel <= last_rel; rel += step_n, t += step_t) {
-                        {
+            for (int cb = 0; cb < P.C; cb += P.NB) {
+                const int nbc = P.C - cb < P.NB ? P.C - cb : P.NB;
+                // ---- stage 1 (A1 + A7/A8) ----
+                if (u < A) {
+                    for (int sl = 0; sl < nbc; ++sl) {
+                        const uint32_t* tw = reinterpret_cast<const uint32_t*>(tiles + (size_t)(cb + sl) * P.tile_stride);
+                        double* pd = s1 + (size_t)sl * P.s1_cap + p0 * P.pitch2 + q0;
+                        int ph = p0, d = d0;
+                        for (int rel = rel0; rel <= last_rel; rel += step_n, d += step_t) {
                             double y = 0.0;                         // pre-stream stage-1 samples are 0.0 (ring zero-init)
-                            if (n_lo + rel >= 0) {
-                                const int d = (int)(t - 31 - 8 * s_lo);   // tile-relative bit of the window's oldest bit
+                            if (rel >= relz) {
                                 const int w = d >> 5;
                                 const uint32_t z = __brev(__funnelshift_r(tw[w], tw[w + 1], d & 31));   // bit j = x[t-j]
                                 y = lds_f64<0>(__dp2a_lo(rlo, z, tpl));
-                                if (gmax > 1) y = __dadd_rn(y, lds_f64<8>(__dp2a_lo(rhi, z, tpl)));
-                                if (gmax > 2) y = __dadd_rn(y, lds_f64<16>(__dp2a_hi(rlo, z, tpl)));
-                                if (gmax > 3) y = __dadd_rn(y, lds_f64<24>(__dp2a_hi(rhi, z, tpl)));
-                                if (gmax > 4) y = __dadd_rn(y, lds_f64<32>(__dp2a_lo(rlo, z, tpl)));   // 8g mod 32: byte 0 again
+                                if (GMAX > 1) y = __dadd_rn(y, lds_f64<8>(__dp2a_lo(rhi, z, tpl)));
+                                if (GMAX > 2) y = __dadd_rn(y, lds_f64<16>(__dp2a_hi(rlo, z, tpl)));
+                                if (GMAX > 3) y = __dadd_rn(y, lds_f64<24>(__dp2a_hi(rhi, z, tpl)));
+                                if (GMAX > 4) y = __dadd_rn(y, lds_f64<32>(__dp2a_lo(rlo, z, tpl)));   // 8g mod 32: byte 0 again
                             }
-                            dst[ph * P.pitch2 + q] = y;
+                            *pd = y;
+                            pd += step_el; ph += step_ph;
+                            if (ph >= P.D2) { ph -= P.D2; pd += wrap_el; }
                         }
-                        q += step_q; ph += step_ph;
-                        if (ph >= P.D2) { ph -= P.D2; ++q; }
                     }
                 }
-            }
-            __syncthreads();
-            // ---- stage 2 (A9) ----
-            for (int item = tid; item < nbc * cnt2; item += blockDim.x) {
-                const int sl = item / cnt2, idx = item - sl * cnt2;
-                const long long k2 = k2_lo + idx;
-                double tot = 0.0;
-                if (k2 >= 0)
-                    tot = fir_sym_t(P.c2, P.off2f, P.off2b, s1 + (size_t)sl * P.s1_cap + (int)(k2 - k2c), P.h2);
-                if (P.nstages == 2) em.emit(P, J, ostage, cb + sl, f0 + idx, idx, tot);
-                else {
-                    const int qq = idx / P.D3;
-                    s2[(size_t)sl * P.s2_cap + (idx - qq * P.D3) * P.pitch3 + qq] = tot;
+                consumer_sync();
+                // ---- stage 2 (A9) ----
+                for (int item = tid; item < nbc * cnt2; item += kLmConsumers) {
+                    int sl = 0, idx = item;
+                    while (idx >= cnt2) { idx -= cnt2; ++sl; }
+                    double tot = 0.0;
+                    if (H.k2_lo + idx >= 0)
+                        tot = fir_sym_t(P.c2, s1 + (size_t)sl * P.s1_cap + (idx + H.j2_0), P.h2, P.D2, P.pitch2, P.sigma2);
+                    if (P.nstages == 2) em.emit(P, J, ostage, cb + sl, f0 + idx, idx, tot);
+                    else {
+                        const int e3 = idx + P.sigma3;
+                        const int qq = (e3 * P.inv_d3) >> 16;
+                        s2[(size_t)sl * P.s2_cap + (e3 - qq * P.D3) * P.pitch3 + qq] = tot;
+                    }
                 }
-            }
-            // ---- stage 3 ----
-            if (P.nstages == 3) {
-                __syncthreads();
-                for (int item = tid; item < nbc * nf; item += blockDim.x) {
-                    const int sl = item / nf, idx = item - sl * nf;
-                    const double y = fir_sym_t(P.c3, P.off3f, P.off3b, s2 + (size_t)sl * P.s2_cap + idx, P.h3);
-                    em.emit(P, J, ostage, cb + sl, f0 + idx, idx, y);
+                // ---- stage 3 ----
+                if (P.nstages == 3) {
+                    consumer_sync();
+                    for (int item = tid; item < nbc * nf; item += kLmConsumers) {
+                        int sl = 0, idx = item;
+                        while (idx >= nf) { idx -= nf; ++sl; }
+                        const double y = fir_sym_t(P.c3, s2 + (size_t)sl * P.s2_cap + idx, P.h3, P.D3, P.pitch3, P.sigma3);
+                        em.emit(P, J, ostage, cb + sl, f0 + idx, idx, y);
+                    }
                 }
+                if (cb + P.NB < P.C) consumer_sync();               // s1/s2 are reused by the next channel group
             }
-            __syncthreads();                                        // s1/s2 are reused by the next channel group
         }
-        if (P.out_format != D2P_DEV_OUT_PLANAR) {
-            const size_t fb = (size_t)P.C * P.bps;
-            copy_out(J.out + (size_t)(f0 - J.f_begin) * fb, ostage, (int)(nf * fb), tid, blockDim.x);
-        }
+        __syncthreads();
     }
-    em.flush(P);
+    if (producer && Hc.J == nullptr && Hp.J && staged_out) {
+        // after the loop Hp is the last tile processed (Hc, the one after it, does not exist)
+        const int jl = (int)((P.total_tiles - 1 - blockIdx.x) / gridDim.x);   // index of this CTA's last tile
+        copy_out(Hp.J->out + (size_t)(Hp.f0 - Hp.J->f_begin) * fb, ostage0 + (size_t)(jl & 1) * P.ostage_bytes,
+                 (int)(Hp.nf * fb), ptid, np);
+    }
+    if (!producer) em.flush(P);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -758,7 +822,11 @@ const char* kernel_name(bool lm) { return lm ? "d2p::lm_kernel" : "d2p::lutfir_k
 // variant: 0 = lm_kernel, 1 = lutfir generic writer, 2/3/4 = lutfir fast 3-byte-LE writer with dither X/T/R
 static const void* kernel_fn(int variant) {
     switch (variant) {
-    case 0: return (const void*)lm_kernel;
+    case 0: case 15: return (const void*)lm_kernel<5>;
+    case 11: return (const void*)lm_kernel<1>;
+    case 12: return (const void*)lm_kernel<2>;
+    case 13: return (const void*)lm_kernel<3>;
+    case 14: return (const void*)lm_kernel<4>;
     case 2: return (const void*)lutfir_kernel<1, 0>;
     case 3: return (const void*)lutfir_kernel<1, 'T'>;
     case 4: return (const void*)lutfir_kernel<1, 'R'>;
@@ -767,13 +835,13 @@ static const void* kernel_fn(int variant) {
 }
 
 int kernel_variant(const KParams& P, bool lm, bool fast_writer_ok) {
-    if (lm) return 0;
+    if (lm) return 10 + (P.gmax < 1 ? 1 : (P.gmax > 5 ? 5 : P.gmax));
     if (!fast_writer_ok) return 1;
     return P.dither == 'T' ? 3 : (P.dither == 'R' ? 4 : 2);
 }
 
 static cudaError_t ensure_smem_attr(int variant) {
-    static bool attr_done[5][64] = {};
+    static bool attr_done[16][64] = {};
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;

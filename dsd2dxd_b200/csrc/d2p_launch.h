@@ -13,6 +13,9 @@ namespace d2p {
 static const int kMaxThreads = 512;          // CTA size of lm_kernel; consumer threads of lutfir_kernel
 static const int kLutfirProducers = 128;     // extra threads of lutfir_kernel that stage tiles and copy results out
 static const int kLutfirThreads = kMaxThreads + kLutfirProducers;
+static const int kLmProducers = 64;          // extra threads of lm_kernel (same role)
+static const int kLmConsumers = 896;         // consumer threads of lm_kernel (stage work)
+static const int kLmThreads = kLmConsumers + kLmProducers;
 static const int kLutPad = 128;              // legacy pad constant (lm_kernel does not use it)
 static const int kMaxSmem = 227 * 1024;      // opt-in dynamic shared memory per CTA on sm_100a
 
