@@ -132,8 +132,6 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
     int st = make_plan(cfg, &dp->plan, &msg);
     if (st != D2P_OK) return set_err(st, msg);
     const Plan& p = dp->plan;
-    if (cfg.dither == D2P_DITHER_FPD)
-        return set_err(D2P_ERR_INVALID_ARG, "dither F (Airwindows float dither) is not implemented on the GPU path yet");
     dp->lm = p.nstages > 1;
 
     int ndev = 0;
@@ -282,6 +280,75 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
 static void free_device_plan(DevicePlan* dp) { delete dp; }
 
 // ------------------------------------------------------------------------------------------------
+// Dither F support: Dither::init_rand seed and the xorshift32 jump tables used by fpd_kernel.
+// ------------------------------------------------------------------------------------------------
+// init_rand (rd/dither.rs:71-76) draws u32s until one is >= 16386; the draws come from Philox4x32-10 with
+// counter (k, 0, 0, 0xF9D) and the 64-bit seed as key -- the same stand-in for thread_rng as oracle/oracle.cpp.
+static uint32_t fpd_init_state(uint64_t seed) {
+    uint32_t fpd = 1;
+    for (uint32_t k = 0; fpd < 16386; ++k) {
+        uint32_t c0 = k, c1 = 0, c2 = 0, c3 = 0xF9Du, k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+        for (int r = 0; r < 10; ++r) {
+            const uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
+            const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0, n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+            c1 = (uint32_t)p1; c3 = (uint32_t)p0; c0 = n0; c2 = n2;
+            k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+        }
+        fpd = c0;
+    }
+    return fpd;
+}
+
+struct Gf2Mat { uint32_t col[32]; };
+static uint32_t gf2_apply(const Gf2Mat& m, uint32_t v) {
+    uint32_t r = 0;
+    for (int i = 0; v; ++i, v >>= 1) if (v & 1u) r ^= m.col[i];
+    return r;
+}
+static Gf2Mat gf2_mul(const Gf2Mat& a, const Gf2Mat& b) {          // a after b
+    Gf2Mat r;
+    for (int i = 0; i < 32; ++i) r.col[i] = gf2_apply(a, b.col[i]);
+    return r;
+}
+// [level][digit][byte][256]: M^(digit * 256^level) applied to (w << 8*byte); M = one xorshift32 (13, 17, 5) step
+static const std::vector<uint32_t>& fpd_jump_tables() {
+    static std::vector<uint32_t> T;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        T.resize((size_t)4 * 256 * 4 * 256);
+        Gf2Mat base;
+        for (int i = 0; i < 32; ++i) { uint32_t x = 1u << i; x ^= x << 13; x ^= x >> 17; x ^= x << 5; base.col[i] = x; }
+        for (int lv = 0; lv < 4; ++lv) {
+            Gf2Mat pw;
+            for (int i = 0; i < 32; ++i) pw.col[i] = 1u << i;       // identity
+            for (int dg = 0; dg < 256; ++dg) {
+                uint32_t* out = &T[((size_t)lv * 256 + dg) << 10];
+                for (int by = 0; by < 4; ++by)
+                    for (uint32_t w = 0; w < 256; ++w) out[by * 256 + w] = gf2_apply(pw, w << (8 * by));
+                pw = gf2_mul(base, pw);
+            }
+            base = pw;                                              // base^256
+        }
+    });
+    return T;
+}
+static int fpd_jump_device(int device, const uint32_t** out) {
+    static std::mutex mu;
+    static std::map<int, uint32_t*> per_dev;
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = per_dev.find(device);
+    if (it == per_dev.end()) {
+        const std::vector<uint32_t>& T = fpd_jump_tables();
+        uint32_t* d = nullptr;
+        CK(cudaMalloc(&d, T.size() * sizeof(uint32_t)));
+        CK(cudaMemcpy(d, T.data(), T.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        it = per_dev.emplace(device, d).first;
+    }
+    *out = it->second;
+    return D2P_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // Launcher: uploads the job table and starts one persistent kernel over all tiles of all jobs.
 // ------------------------------------------------------------------------------------------------
 struct Launcher {
@@ -293,6 +360,8 @@ struct Launcher {
     int next = 0;
     DevStats* d_stats = nullptr;
     ClipEvent* d_events = nullptr;
+    uint32_t* d_fpd[kRing] = {nullptr, nullptr, nullptr, nullptr};   // dither F: per-sample xorshift32 states of a launch
+    size_t fpd_cap[kRing] = {0, 0, 0, 0};
     uint64_t launches = 0;
 
     int init(bool want_events) {
@@ -307,17 +376,47 @@ struct Launcher {
             if (h_jobs[i]) cudaFreeHost(h_jobs[i]);
             if (d_jobs[i]) cudaFree(d_jobs[i]);
             if (ev[i]) cudaEventDestroy(ev[i]);
+            if (d_fpd[i]) cudaFree(d_fpd[i]);
         }
         if (d_stats) cudaFree(d_stats);
         if (d_events) cudaFree(d_events);
     }
 
-    // jobs[i].tile_begin / job_id are filled here.  Asynchronous on `stream`.
+    // Dither F needs 4 bytes of xorshift state per output sample of a launch: long jobs are cut into pieces of at
+    // most kFpdSamples samples, launched one group after the other on the same stream (the buffer is reused).
+    static const long long kFpdSamples = 256ll << 20;
     int run(const DevicePlan& dp, std::vector<DevJob>& jobs, cudaStream_t stream) {
+        for (size_t i = 0; i < jobs.size(); ++i) jobs[i].job_id = (int)i;
+        if (dp.plan.cfg.dither != D2P_DITHER_FPD) return run_once(dp, jobs, stream, false);
+        const d2p_config& c = dp.plan.cfg;
+        const long long cap_frames = std::max<long long>(kFpdSamples / c.channels, dp.kp.TF);
+        const bool planar_out = c.out_format == D2P_OUT_PLANAR_32;
+        std::vector<DevJob> group;
+        long long used = 0;
+        for (const DevJob& j : jobs) {
+            for (long long off = 0; off < j.f_count;) {
+                const long long take = std::min(j.f_count - off, cap_frames - used);
+                DevJob pc = j;
+                pc.f_begin = j.f_begin + off; pc.f_count = take;
+                pc.out = j.out + (size_t)off * (planar_out ? 4 : (size_t)c.channels * dp.plan.bps);
+                if (j.f64) pc.f64 = j.f64 + off;
+                group.push_back(pc);
+                off += take; used += take;
+                if (used >= cap_frames) {
+                    int st = run_once(dp, group, stream, true);
+                    if (st != D2P_OK) return st;
+                    group.clear(); used = 0;
+                }
+            }
+        }
+        return group.empty() ? D2P_OK : run_once(dp, group, stream, true);
+    }
+
+    // jobs[i].tile_begin is filled here.  Asynchronous on `stream`.
+    int run_once(const DevicePlan& dp, std::vector<DevJob>& jobs, cudaStream_t stream, bool fpd) {
         unsigned long long tiles = 0;
         std::vector<DevJob> live;
         for (size_t i = 0; i < jobs.size(); ++i) {
-            jobs[i].job_id = (int)i;
             if (jobs[i].f_count <= 0) continue;
             jobs[i].tile_begin = (unsigned int)tiles;
             tiles += (unsigned long long)((jobs[i].f_count + dp.kp.TF - 1) / dp.kp.TF);
@@ -334,9 +433,38 @@ struct Launcher {
             CK(cudaMallocHost(&h_jobs[slot], sizeof(DevJob) * cap[slot]));
             CK(cudaMalloc(&d_jobs[slot], sizeof(DevJob) * cap[slot]));
         }
+        KParams k = dp.kp;
+        k.fpd_jump = nullptr; k.fpd_items = 0;
+        if (fpd) {
+            const Plan& p = dp.plan;
+            const long long B = p.cfg.block_size;
+            size_t samples = 0;
+            unsigned long long items = 0;
+            for (DevJob& j : live) samples += (size_t)j.f_count * p.cfg.channels;
+            if (fpd_cap[slot] < samples) {
+                if (d_fpd[slot]) cudaFree(d_fpd[slot]);
+                fpd_cap[slot] = samples + samples / 8 + 1024;
+                CK(cudaMalloc(&d_fpd[slot], fpd_cap[slot] * sizeof(uint32_t)));
+            }
+            size_t at = 0;
+            for (DevJob& j : live) {
+                j.fpd = d_fpd[slot] + at; j.fpd_stride = j.f_count;
+                at += (size_t)j.f_count * p.cfg.channels;
+                if (j.total_q <= 0) j.total_q = LLONG_MAX;
+                j.blk_lo = (p.bytes_needed_for_frames(j.f_begin + 1) - 1) / B;
+                const long long blk_hi = (p.bytes_needed_for_frames(j.f_begin + j.f_count) - 1) / B;
+                j.nblk = (int)(blk_hi - j.blk_lo + 1);
+                j.fpd_item_begin = (unsigned int)items;
+                items += (unsigned long long)j.nblk * p.cfg.channels;
+                j.fpd0 = fpd_init_state(j.seed);
+            }
+            if (items > 0xFFFFFFF0ull) return set_err(D2P_ERR_INVALID_ARG, "too many dither work items in one launch");
+            k.fpd_items = (unsigned int)items;
+            int st = fpd_jump_device(p.cfg.device, &k.fpd_jump);
+            if (st != D2P_OK) return st;
+        }
         std::memcpy(h_jobs[slot], live.data(), sizeof(DevJob) * live.size());
         CK(cudaMemcpyAsync(d_jobs[slot], h_jobs[slot], sizeof(DevJob) * live.size(), cudaMemcpyHostToDevice, stream));
-        KParams k = dp.kp;
         k.jobs = d_jobs[slot];
         k.njobs = (int)live.size();
         k.total_tiles = (unsigned int)tiles;
@@ -345,6 +473,7 @@ struct Launcher {
         k.ev_cap = d_events ? kEventCap : 0;
         const unsigned long long want = (unsigned long long)dp.num_sms * dp.ctas_per_sm;
         const int grid = (int)std::min<unsigned long long>(tiles, want);
+        if (fpd) CK(launch_fpd(k, stream));
         bool fast = dp.fast_writer;
         for (const DevJob& j : live) if (j.f64) fast = false;
         CK(launch_kernels(k, kernel_variant(k, dp.lm, fast), grid, dp.threads, dp.smem, stream));
@@ -464,9 +593,13 @@ static int ctx_collect_events(d2p_ctx* ctx) {
 }
 
 // Launch everything computable from the bytes now resident: [frames_done, frames_for_bytes(end_q)).
-static int ctx_process(d2p_ctx* ctx, long long end_q, long long tail_q, long long tail_len) {
+static int ctx_process(d2p_ctx* ctx, long long end_q, long long tail_q, long long tail_len, bool final) {
     const Plan& p = ctx->dp->plan;
-    const long long f_new = p.frames_for_bytes(end_q);
+    // Dither F numbers the samples in reader order (block, channel, frame): a block's frames can only be placed
+    // once the block is complete (or the stream has ended), so an unfinished block is held back.
+    long long upto_q = end_q;
+    if (p.cfg.dither == D2P_DITHER_FPD && !final) upto_q = end_q / p.cfg.block_size * p.cfg.block_size;
+    const long long f_new = p.frames_for_bytes(upto_q);
     const long long cnt = f_new - ctx->frames_done;
     if (cnt <= 0) return D2P_OK;
     OutChunk oc;
@@ -483,6 +616,7 @@ static int ctx_process(d2p_ctx* ctx, long long end_q, long long tail_q, long lon
     j.out = oc.d_pcm; j.out_stride = cnt;
     j.f64 = oc.d_f64; j.f64_stride = cnt;
     j.seed = p.cfg.dither_seed;
+    j.total_q = final ? end_q : LLONG_MAX;
     int st = ctx->launcher.run(*ctx->dp, jobs, ctx->stream);
     if (st != D2P_OK) return st;
     ctx->frames_done = f_new;
@@ -630,7 +764,7 @@ int d2p_push(d2p_ctx* ctx, const uint8_t* raw, size_t nbytes) {
     CK(cudaStreamSynchronize(ctx->stream));            // `raw` and `pending` may be reused by the caller after return
     ctx->pending.assign(raw + from_raw, raw + nbytes);
     ctx->have_q += (long long)(whole / c.channels);
-    return ctx_process(ctx, ctx->have_q, LLONG_MAX, 0);
+    return ctx_process(ctx, ctx->have_q, LLONG_MAX, 0, false);
 }
 
 int d2p_finish(d2p_ctx* ctx) {
@@ -640,7 +774,7 @@ int d2p_finish(d2p_ctx* ctx) {
     const d2p_config& c = ctx->dp->plan.cfg;
     CK(cudaSetDevice(c.device));
     const size_t per = ctx->pending.size() / c.channels;      // trailing partial group: split evenly (A1)
-    if (per == 0) return D2P_OK;
+    if (per == 0) return ctx_process(ctx, ctx->have_q, LLONG_MAX, 0, true);   // frames held back for dither F
     const size_t take = per * c.channels;
     uint8_t* dst = nullptr;
     int st = ctx_prepare_input(ctx, take, &dst);
@@ -650,8 +784,8 @@ int d2p_finish(d2p_ctx* ctx) {
     const long long tail_q = ctx->have_q;
     ctx->have_q += (long long)per;
     ctx->pending.clear();
-    if (c.in_layout == D2P_LAYOUT_PLANAR) return ctx_process(ctx, ctx->have_q, tail_q, (long long)per);
-    return ctx_process(ctx, ctx->have_q, LLONG_MAX, 0);
+    if (c.in_layout == D2P_LAYOUT_PLANAR) return ctx_process(ctx, ctx->have_q, tail_q, (long long)per, true);
+    return ctx_process(ctx, ctx->have_q, LLONG_MAX, 0, true);
 }
 
 uint64_t d2p_frames_ready(const d2p_ctx* ctx) { return ctx ? (uint64_t)(ctx->frames_done - ctx->frames_pulled) : 0; }
@@ -848,7 +982,7 @@ static int host_convert(const DevicePlan& dp, Launcher& launcher, HostPipe& pipe
             j.in = pipe.d_in[s]; j.base_q = gk * unit; j.end_q = end_q;
             j.tail_q = (last && tail_per > 0 && planar) ? groups * unit : LLONG_MAX; j.tail_len = tail_per;
             j.f_begin = f_done; j.f_count = f_new - f_done;
-            j.out = pipe.d_out[s]; j.seed = c.dither_seed;
+            j.out = pipe.d_out[s]; j.seed = c.dither_seed; j.total_q = total_q;
             if ((size_t)j.f_count * fb > pipe.out_cap) { rc = set_err(D2P_ERR_NOMEM, "internal: chunk output larger than staging buffer"); break; }
             if ((rc = launcher.run(dp, jobs, pipe.streams[s])) != D2P_OK) break;
             e = cudaMemcpyAsync((uint8_t*)pcm + (size_t)f_done * fb, pipe.d_out[s], (size_t)j.f_count * fb, cudaMemcpyDeviceToHost, pipe.streams[s]);
@@ -945,7 +1079,7 @@ int d2p_batch_run(d2p_batch* b, d2p_job* jobs, int njobs, void* cuda_stream) {
         j.f_begin = 0; j.f_count = nf;
         j.out = (uint8_t*)u.d_out; j.out_stride = nf;
         j.f64 = u.d_f64; j.f64_stride = (long long)u.f64_stride;
-        j.seed = u.dither_seed;
+        j.seed = u.dither_seed; j.total_q = total_q;
         u.frames = (uint64_t)nf;
     }
     return b->launcher.run(*b->dp, dj, (cudaStream_t)cuda_stream);
@@ -1005,7 +1139,7 @@ int d2p_batch_run_blocks(d2p_batch* b, const d2p_block_job* jobs, int njobs, voi
         j.f_begin = (long long)u.first_frame; j.f_count = (long long)u.frame_count;
         j.out = (uint8_t*)u.d_out; j.out_stride = (long long)u.frame_count;
         j.f64 = u.d_f64; j.f64_stride = (long long)u.f64_stride;
-        j.seed = u.dither_seed;
+        j.seed = u.dither_seed; j.total_q = g.total_q;
     }
     return b->launcher.run(*b->dp, dj, (cudaStream_t)cuda_stream);
 }

@@ -21,6 +21,16 @@ struct DevJob {
     unsigned long long seed;  // dither key
     unsigned int tile_begin;  // first global tile index of this job
     int job_id;
+    // Airwindows float dither (-d F): the reference's xorshift32 state is sequential over the samples in reader
+    // order (block, channel, frame).  fpd_kernel materialises the state of every sample of the job first.
+    uint32_t* fpd;            // [channel * fpd_stride + (frame - f_begin)], or null
+    long long fpd_stride;
+    long long total_q;        // per-channel bytes of the whole stream if the job reaches its last block, else LLONG_MAX
+    long long blk_lo;         // reader block holding frame f_begin
+    unsigned int fpd_item_begin;   // first (block, channel) work item of this job; nblk * C items
+    int nblk;
+    uint32_t fpd0;            // state after Dither::init_rand
+    int pad0;
 };
 
 struct DevStats {
@@ -81,6 +91,9 @@ struct KParams {
     long long lm_base_hi;     // high-rate index of stage-1 output 0
     long long lm_step_t;      // input-time step of one half-warp iteration: m1 * A * (threads/16) / L
     unsigned char groups[kMaxPhasesDev];
+
+    const uint32_t* fpd_jump; // xorshift32 jump tables: [level 0..3][digit 0..255][byte 0..3][256] (4 MiB), or null
+    unsigned int fpd_items;
 
     DevStats* stats;
     ClipEvent* events;

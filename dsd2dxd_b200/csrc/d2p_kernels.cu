@@ -15,6 +15,7 @@
 // Bit-exactness: every f64 operation is an explicit __dadd_rn/__dmul_rn in the reference's order
 // (left folds; no FMA contraction; the file is also compiled with -fmad=false).
 #include <cuda_runtime.h>
+#include <limits.h>
 #include <stdint.h>
 
 #include "d2p_device.h"
@@ -244,6 +245,19 @@ struct Emitter {
         if (P.has_ds) s = __dmul_rn(s, P.neg_scale);            // Dither::process_samp rd/dither.rs:86-95
         if (P.dither == 'T' || P.dither == 'R')
             s = __dadd_rn(s, dither_noise(P.dither, (unsigned long long)f, (uint32_t)ch, key));
+        else if (P.dither == 'F' && J.fpd) {                    // Dither::fpdither  rd/dither.rs:102-110
+            const uint32_t fpd = J.fpd[(long long)ch * J.fpd_stride + fj];
+            const double l2 = floor(log2(fabs(s)));
+            int e;                                              // Rust `as i32`: NaN -> 0, saturating
+            if (l2 != l2) e = 0;
+            else if (l2 <= -2147483648.0) e = INT_MIN;
+            else if (l2 >= 2147483647.0) e = INT_MAX;
+            else e = (int)l2;
+            long long e2 = (long long)e + 62;
+            e2 = e2 > 4096 ? 4096 : (e2 < -4096 ? -4096 : e2);   // 2^e2 is 0 / inf beyond the f64 range either way
+            s = __dadd_rn(s, __dmul_rn(__dmul_rn((double)fpd, 3.4e-36), ldexp(1.0, (int)e2)));
+            s = (double)__double2float_rn(s);
+        }
         if (P.has_ds) s = __dmul_rn(s, P.pos_scale);
 
         if (P.bits == 32) {
@@ -815,6 +829,69 @@ __global__ void __launch_bounds__(kLmThreads) lm_kernel(const __grid_constant__ 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Airwindows float dither (-d F, the CLI default for 32-bit float output): Dither::fpd is ONE xorshift32
+// stream per file, advanced once per sample in reader order -- block, then channel, then frame
+// (rd/conversion_context.rs:303-315, rd/pcm_writer.rs:608-648).  Sample number n of the file (0-based) sees the
+// state after n+1 steps.  xorshift32 is linear over GF(2), so a work item jumps straight to the state in
+// front of its run of samples with four byte-sliced matrix applications (P.fpd_jump), then walks the run.
+// One work item = the frames one channel gets out of one reader block.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ long long dev_frames_for_bytes(const KParams& P, long long bytes) {   // Plan::frames_for_bytes
+    if (bytes <= 0) return 0;
+    if (P.nstages == 1) { const long long f = bytes / P.bpo - (P.h - 1); return f > 0 ? f : 0; }
+    const long long hi = bytes * 8 * P.L;
+    long long n1 = P.accum ? hi / 21 - P.e0 : (hi >= P.h1 ? (hi - P.h1) / P.m1 : 0);
+    if (n1 < 0) n1 = 0;
+    const long long n2 = n1 >= P.h2 ? (n1 - P.h2) / P.D2 + 1 : 0;
+    if (P.nstages == 2) return n2;
+    return n2 >= P.h3 ? (n2 - P.h3) / P.D3 + 1 : 0;
+}
+
+__device__ __forceinline__ uint32_t fpd_jump(const uint32_t* __restrict__ T, uint32_t s, unsigned long long steps) {
+    const uint32_t n = (uint32_t)(steps % 4294967295ull);           // the period of xorshift32 is 2^32 - 1
+#pragma unroll
+    for (int lv = 0; lv < 4; ++lv) {
+        const uint32_t dg = (n >> (8 * lv)) & 255u;
+        if (dg) {
+            const uint32_t* M = T + ((size_t)(lv * 256 + dg) << 10);
+            s = M[s & 255u] ^ M[256 + ((s >> 8) & 255u)] ^ M[512 + ((s >> 16) & 255u)] ^ M[768 + (s >> 24)];
+        }
+    }
+    return s;
+}
+
+__global__ void __launch_bounds__(256) fpd_kernel(const __grid_constant__ KParams P) {
+    const unsigned int item = blockIdx.x * blockDim.x + threadIdx.x;
+    if (item >= P.fpd_items) return;
+    int lo = 0, hi = P.njobs - 1;
+    while (lo < hi) {                      // last job with fpd_item_begin <= item
+        const int mid = (lo + hi + 1) >> 1;
+        if (P.jobs[mid].fpd_item_begin <= item) lo = mid; else hi = mid - 1;
+    }
+    const DevJob& J = P.jobs[lo];
+    if (!J.fpd) return;
+    const unsigned int li = item - J.fpd_item_begin;
+    const int c = (int)(li % (unsigned int)P.C);
+    const long long blk = J.blk_lo + (long long)(li / (unsigned int)P.C);
+    const long long B = P.block_size;
+    const long long f_before = dev_frames_for_bytes(P, blk * B);
+    long long q_end = (blk + 1) * B;
+    if (q_end > J.total_q) q_end = J.total_q;
+    const long long f_after = dev_frames_for_bytes(P, q_end);
+    const long long run = f_after - f_before;
+    long long fs = f_before > J.f_begin ? f_before : J.f_begin;
+    long long fe = f_after < J.f_begin + J.f_count ? f_after : J.f_begin + J.f_count;
+    if (fs >= fe) return;
+    const unsigned long long n0 = (unsigned long long)P.C * f_before + (unsigned long long)c * run + (fs - f_before);
+    uint32_t s = fpd_jump(P.fpd_jump, J.fpd0, n0);
+    uint32_t* dst = J.fpd + (long long)c * J.fpd_stride + (fs - J.f_begin);
+    for (long long f = fs; f < fe; ++f) {
+        s ^= s << 13; s ^= s >> 17; s ^= s << 5;
+        *dst++ = s;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // host launcher
 // ------------------------------------------------------------------------------------------------
 const char* kernel_name(bool lm) { return lm ? "d2p::lm_kernel" : "d2p::lutfir_kernel"; }
@@ -860,6 +937,12 @@ int max_ctas_per_sm(bool lm, int threads, size_t smem) {
     int n = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel_fn(variant), threads, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
     return n;
+}
+
+cudaError_t launch_fpd(const KParams& P, cudaStream_t stream) {
+    if (!P.fpd_items) return cudaSuccess;
+    fpd_kernel<<<(P.fpd_items + 255) / 256, 256, 0, stream>>>(P);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_kernels(const KParams& P, int variant, int grid, int threads, size_t smem, cudaStream_t stream) {

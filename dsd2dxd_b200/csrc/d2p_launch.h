@@ -22,6 +22,7 @@ static const int kMaxSmem = 227 * 1024;      // opt-in dynamic shared memory per
 const char* kernel_name(bool lm);
 int max_ctas_per_sm(bool lm, int threads, size_t smem);   // occupancy of the kernel at this geometry (0 on error)
 int kernel_variant(const KParams& P, bool lm, bool fast_writer_ok);   // which instantiation a launch uses
+cudaError_t launch_fpd(const KParams& P, cudaStream_t stream);     // per-sample xorshift32 states for dither F
 cudaError_t launch_kernels(const KParams& P, int variant, int grid, int threads, size_t smem, cudaStream_t stream);
 
 }  // namespace d2p

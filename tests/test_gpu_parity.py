@@ -261,3 +261,46 @@ def test_time_blocks_on_device_equal_one_pass(kw):
     got = np.concatenate([o.cpu().numpy()[:b.frame_count * C * bps] for b, o in zip(blocks, d_out)])
     assert np.array_equal(got, ref.pcm)
     batch.close()
+
+
+@pytest.mark.parametrize("out_rate,bits", [(352800, 32), (352800, 24), (88200, 16), (192000, 32), (96000, 24), (384000, 32)])
+@pytest.mark.parametrize("layout,channels", [("P", 2), ("I", 3)])
+def test_fpd_dither_matches_reference_order(out_rate, bits, layout, channels):
+    """Dither F (A15): one xorshift32 stream per file in reader order (block, channel, frame) -- the GPU jumps
+    to every run's state; one-shot, ragged streaming pushes and the pipelined host path all agree with the oracle."""
+    raw = rand_payload(out_rate % 89 + bits, channels, 5)[: channels * (4 * 4096 + 1234)]
+    kw = dict(dsd_rate=1, out_rate=out_rate, bits=bits, channels=channels, layout=layout, lsb_first=(layout == "P"),
+              dither="F", dither_seed=0xABCDEF12345)
+    ref = orclib.convert(raw, want_f64=False, **kw)
+    pcm, _, _ = run_gpu(raw, **kw)
+    assert np.array_equal(pcm, ref.pcm)
+    cuts = [5, 4096 * channels + 7, 9000 * channels, 3 * 4096 * channels - 1]
+    pcm2, _, _ = run_gpu(raw, chunks=cuts, **kw)
+    assert np.array_equal(pcm2, ref.pcm)
+    cfg = d2p.make_config(**kw)
+    pcm3, frames, _ = d2p.convert_host(cfg, raw)
+    assert frames == ref.frames[0] and np.array_equal(pcm3, ref.pcm)
+    clean = orclib.convert(raw, want_f64=False, **dict(kw, dither="X")).pcm
+    assert not np.array_equal(clean, ref.pcm) or bits != 32        # the float dither really changes f32 output
+
+
+def test_fpd_dither_time_blocks_and_long_jump():
+    """Blocks of one file converted independently still see the file's single noise stream."""
+    torch = pytest.importorskip("torch")
+    from dsd2dxd_b200 import shard
+    kw = dict(dsd_rate=4, out_rate=352800, bits=32, channels=2, layout="P", lsb_first=True, dither="F", dither_seed=99)
+    raw = rand_payload(4242, 2, 70)
+    cfg = d2p.make_config(**kw)
+    ref = orclib.convert(raw, want_f64=False, **kw)
+    blocks = shard.split_payload(cfg, raw.size, 5)
+    batch = d2p.Batch(cfg)
+    d_in = [torch.from_numpy(raw[b.in_offset:b.in_offset + b.in_bytes].copy()).cuda() for b in blocks]
+    d_out = [torch.zeros(b.frame_count * 8 + 16, dtype=torch.uint8, device="cuda") for b in blocks]
+    batch.run_blocks([dict(d_in=i.data_ptr(), in_offset=b.in_offset, in_bytes=b.in_bytes, payload_bytes=raw.size,
+                           first_frame=b.first_frame, frame_count=b.frame_count, d_out=o.data_ptr(),
+                           out_cap_bytes=o.numel(), dither_seed=99) for b, i, o in zip(blocks, d_in, d_out)],
+                     torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    got = np.concatenate([o.cpu().numpy()[:b.frame_count * 8] for b, o in zip(blocks, d_out)])
+    assert np.array_equal(got, ref.pcm)
+    batch.close()
