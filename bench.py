@@ -231,6 +231,20 @@ def main():
     lookups = args.files * in_bytes * (2 * ((info["half_taps"][0] + 7) // 8)) / (info["decims"][0] // 8)
     sm_mhz = clocks["sm_mhz"] or pk.get("sm_max_mhz", 1965.0)
     lds_peak = SM_COUNT * LDS_LOOKUPS_PER_CLK_SM * pk.get("sm_max_mhz", 1965.0) * 1e6
+    lds_kind = "nominal 16 lookups/clk/SM x 148 SM x max SM clock"
+    try:        # measured on this pool's B200 by tools/microbench.cu (conflict-free LDS.64 look-ups)
+        mb = json.load(open(os.path.join(ROOT, "profiles", "r01_microbench.json")))
+        lds_peak = float(mb["lds64_lookups_per_s"])
+        lds_kind = "measured: tools/microbench.cu on B200 (profiles/r01_microbench.json)"
+    except Exception:
+        pass
+    traffic = None
+    try:        # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this very command (ncu --set full)
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r01_bench_traffic.json")))
+        if tr.get("files_per_gpu") == args.files and tr.get("minutes_per_file") == args.minutes and tr.get("dither") == args.dither:
+            traffic = tr["dram_bytes_per_launch"]
+    except Exception:
+        pass
 
     if rank == 0:
         line = {
@@ -245,11 +259,12 @@ def main():
             "gpu_launches": int(launches),
             "kernel": "d2p::lutfir_kernel", "kernel_ms": kernel_ms,
             "roofline": {"bound": "hbm", "achieved": alg_bytes / (kernel_ms / 1e3) / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                         "frac": alg_bytes / (kernel_ms / 1e3) / 1e9 / pk["hbm_gbs"], "traffic": None, "peak_kind": pk_kind,
+                         "frac": alg_bytes / (kernel_ms / 1e3) / 1e9 / pk["hbm_gbs"], "traffic": traffic,
+                         "algorithmic_bytes": alg_bytes, "peak_kind": pk_kind,
                          "note": "HBM is not the binding unit of this path (SURVEY.md 8d): see lds"},
             "lds": {"bound": "shared-memory LUT look-ups (8 B each)", "achieved": lookups / (kernel_ms / 1e3),
                     "peak": lds_peak, "unit": "lookups/s", "frac": lookups / (kernel_ms / 1e3) / lds_peak,
-                    "peak_kind": "nominal 16 lookups/clk/SM x 148 SM x max SM clock",
+                    "peak_kind": lds_kind, "lookups_per_launch": lookups,
                     "frac_at_observed_clock": lookups / (kernel_ms / 1e3) / (SM_COUNT * LDS_LOOKUPS_PER_CLK_SM * sm_mhz * 1e6)},
             "clocks": clocks,
         }

@@ -34,3 +34,12 @@ if [[ $SEC == *l* ]]; then
   tail -2 gpurun_out/ncu_l_$TAG.log
 fi
 ls -la gpurun_out | tail -20
+if [[ $SEC == *B* ]]; then   # ncu of the bench command itself: launch list + full capture of one timed launch
+  python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/bench_plain_$TAG.json 2>&1 &&
+  ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/bench_launches_$TAG.csv \
+      python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/bench_ncu1_$TAG.log 2>&1
+  python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/bench_plain2_$TAG.json 2>&1 &&
+  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:lutfir -s 3 -c 1 -f -o gpurun_out/bench_${TAG}_full \
+      python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/bench_ncu2_$TAG.log 2>&1
+  tail -2 gpurun_out/bench_ncu2_$TAG.log
+fi
