@@ -32,6 +32,11 @@ __device__ __forceinline__ uint4 ld_nc_v4(const void* p) {
                  : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
     return r;
 }
+// 16-byte asynchronous global -> shared copy (LDGSTS): the issuing warp does not wait for HBM
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 __device__ __forceinline__ uint32_t bitrev_each_byte(uint32_t w) {   // MSB-first -> LSB-first
     return __byte_perm(__brev(w), 0, 0x0123);
 }
@@ -161,6 +166,10 @@ __device__ void stage_input(const KParams& P, const DevJob& J, unsigned char* ti
             const long long q = s_lo + 16LL * idx;
             uint4 val = make_uint4(0, 0, 0, 0);
             if (fast && q >= J.base_q && q + 16 <= J.end_q && q + 16 <= J.tail_q) {
+                if (P.lsb_first) {         // no transformation needed: asynchronous copy, completed by cp_async_wait_all()
+                    cp_async16(tiles + (size_t)c * P.tile_stride + 16 * idx, J.in + planar_offset(P, J, c, q));
+                    continue;
+                }
                 val = ld_nc_v4(J.in + planar_offset(P, J, c, q));
             } else if (q + 16 > 0 && q < J.end_q) {
                 uint32_t w[4] = {0, 0, 0, 0};
@@ -529,6 +538,7 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
     if (tile < P.total_tiles && producer) {
         const TileInfo t = lutfir_tile(P, tile);
         stage_input(P, *t.J, inbuf, t.s_lo, t.nbytes, ptid, np);
+        cp_async_wait_all();
     }
     __syncthreads();
 
@@ -547,6 +557,7 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
             if (have_prev && staged_out)
                 copy_out(prev.J->out + (size_t)(prev.f0 - prev.J->f_begin) * fb, obuf + (size_t)(bsel ^ 1) * P.ostage_bytes,
                          (int)(prev.nf * fb), ptid, np);
+            cp_async_wait_all();
         } else {
             const unsigned char* tiles = inbuf + (size_t)bsel * P.in_buf_bytes;
             unsigned char* ostage = obuf + (size_t)bsel * P.ostage_bytes;
@@ -733,6 +744,7 @@ __global__ void __launch_bounds__(kLmThreads) lm_kernel(const __grid_constant__ 
         lm_tile_header(P, tile, Hc);
         if (ptid == 0) hdr[0] = Hc;
         stage_input(P, *Hc.J, tiles0, Hc.s_lo, Hc.nbytes, ptid, np);
+        cp_async_wait_all();
     }
     __syncthreads();
 
@@ -750,6 +762,7 @@ __global__ void __launch_bounds__(kLmThreads) lm_kernel(const __grid_constant__ 
                 copy_out(Hp.J->out + (size_t)(Hp.f0 - Hp.J->f_begin) * fb, ostage0 + (size_t)(bsel ^ 1) * P.ostage_bytes,
                          (int)(Hp.nf * fb), ptid, np);
             Hp = Hc; Hc = Hn;
+            cp_async_wait_all();
         } else {
             const LmTile& H = hdr[bsel];
             const DevJob& J = *H.J;
