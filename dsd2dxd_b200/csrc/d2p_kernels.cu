@@ -228,24 +228,29 @@ struct Emitter {
         }
     }
 
+    // WM == 1 in two halves, so that a caller can run the pure arithmetic of several samples side by side:
+    // quant = scale, level, dither, round (no memory access, no branch); put = clamp, clip statistics, pack.
+    __device__ __forceinline__ int quant(const KParams& P, int ch, long long f, double y) {
+        double s = __dmul_rn(y, P.scale);                       // scale_and_dither  rd/pcm_writer.rs:651
+        const unsigned long long ab = (unsigned long long)__double_as_longlong(fabs(s));
+        peakb = ab > peakb ? ab : peakb;                        // process_levels    rd/conversion_context.rs:235-240
+        if (DITH) s = __dadd_rn(s, dither_noise(DITH, (unsigned long long)f, (uint32_t)ch, key));
+        // quantize / my_round   rd/pcm_writer.rs:678-705 ; floor fused into the conversion
+        return __double2int_rd(__dadd_rn(s, s < 0.0 ? -0.5 : 0.5));
+    }
+    __device__ __forceinline__ void put(const KParams& P, const DevJob& J, unsigned char* ostage, int ch, long long f, int fl, int v) {
+        const int mn = -P.peak, mx = P.peak - 1;                // clamp_value  rd/pcm_writer.rs:685
+        if (v < mn) { v = mn; clip_event(P, J, ch, f, 0); }
+        else if (v > mx) { v = mx; clip_event(P, J, ch, f, 1); }
+        const unsigned int u = (unsigned int)v << P.shl20;      // 20-bit: left-aligned in the 3-byte container
+        unsigned char* o = ostage + (fl * P.C + ch) * 3;        // pack_int  rd/pcm_writer.rs:372-396
+        o[0] = (unsigned char)u; o[1] = (unsigned char)(u >> 8); o[2] = (unsigned char)(u >> 16);
+    }
+
     // y: decimator output of channel ch, absolute frame f; fl: frame index inside the tile
     __device__ __forceinline__ void emit(const KParams& P, const DevJob& J, unsigned char* ostage,
                                          int ch, long long f, int fl, double y) {
-        if (WM == 1) {
-            double s = __dmul_rn(y, P.scale);                   // scale_and_dither  rd/pcm_writer.rs:651
-            const unsigned long long ab = (unsigned long long)__double_as_longlong(fabs(s));
-            peakb = ab > peakb ? ab : peakb;                    // process_levels    rd/conversion_context.rs:235-240
-            if (DITH) s = __dadd_rn(s, dither_noise(DITH, (unsigned long long)f, (uint32_t)ch, key));
-            // quantize / my_round / clamp_value   rd/pcm_writer.rs:678-705 ; floor fused into the conversion
-            int v = __double2int_rd(__dadd_rn(s, s < 0.0 ? -0.5 : 0.5));
-            const int mn = -P.peak, mx = P.peak - 1;
-            if (v < mn) { v = mn; clip_event(P, J, ch, f, 0); }
-            else if (v > mx) { v = mx; clip_event(P, J, ch, f, 1); }
-            const unsigned int u = (unsigned int)v << P.shl20;  // 20-bit: left-aligned in the 3-byte container
-            unsigned char* o = ostage + (fl * P.C + ch) * 3;    // pack_int  rd/pcm_writer.rs:372-396
-            o[0] = (unsigned char)u; o[1] = (unsigned char)(u >> 8); o[2] = (unsigned char)(u >> 16);
-            return;
-        }
+        if (WM == 1) { put(P, J, ostage, ch, f, fl, quant(P, ch, f, y)); return; }
         const long long fj = f - J.f_begin;
         if (J.f64) J.f64[(long long)ch * J.f64_stride + fj] = y;
         double s = __dmul_rn(y, P.scale);                       // scale_and_dither  rd/pcm_writer.rs:651
@@ -395,51 +400,36 @@ __device__ __forceinline__ double lds_f64(uint32_t saddr) {
 //               pitch 0 and slot + dz: it reads 0.0 from the SAME bank pair the live look-up would have
 //               hit, so idle lanes never add wavefronts, and acc + 0.0 == acc exactly (acc is never -0.0:
 //               it starts at +0.0 and x + y is -0.0 only if both are).
-struct LaneLut { uint32_t rlo, rhi; int dz; };
-
-template <bool GUARD, int D>
-__device__ __forceinline__ void lutfir_step(const LaneLut& L, uint32_t tp, uint32_t qf, uint32_t qb, int i0, int nt, double& acc) {
-    uint32_t rsel = (D & 1) ? L.rlo : L.rhi;
-    uint32_t t = tp;
-    if (GUARD) {
-        const bool live = (unsigned)(i0 + D) < (unsigned)nt;
-        rsel = live ? rsel : 0u;
-        t = live ? tp : tp + (uint32_t)L.dz;
-    }
-    const uint32_t af = D < 2 ? __dp2a_hi(rsel, qf, t) : __dp2a_lo(rsel, qf, t);
-    const uint32_t ab = D < 2 ? __dp2a_hi(rsel, qb, t) : __dp2a_lo(rsel, qb, t);
-    const double tf = lds_f64<8 * D>(af);
-    const double tb = lds_f64<8 * D>(ab);
-    acc = __dadd_rn(__dadd_rn(acc, tf), tb);
-}
-
-template <bool GUARD>
-__device__ __forceinline__ void lutfir_group(const LaneLut& L, uint32_t tp, uint32_t qf, uint32_t qb, int i0, int nt, double& acc) {
-    lutfir_step<GUARD, 0>(L, tp, qf, qb, i0, nt, acc);
-    lutfir_step<GUARD, 1>(L, tp, qf, qb, i0, nt, acc);
-    lutfir_step<GUARD, 2>(L, tp, qf, qb, i0, nt, acc);
-    lutfir_step<GUARD, 3>(L, tp, qf, qb, i0, nt, acc);
-}
+struct LaneLut { uint32_t rlo, rhi; int dz, c; };
 
 // Two frames (A, B) of one lane in lockstep.  Both frames sit at the same table index at every step, so
 // the skew guard, the slot address and the loop bookkeeping are paid once per pair, and the two dependent
 // DADD chains interleave (ILP 2).  B's bytes are A's bytes dW words further on (same byte alignment).
-// tw: A's channel tile as words; jr: tile-relative index of A's newest byte; c: the lane's skew;
-// tp0: shared-memory address of the lane's slot at step 0.
+// K: where frame A starts; tp0: shared-memory address of the lane's slot at step 0.
 // PAIR = false: frame A alone (tiles too small to give every consumer thread two frames).
+//
+// Where a lane's frame starts in its channel tile: word pointers and funnel shifts of the two byte streams.
+//   forward half : step u reads byte jr + c - u  (group g: bytes a-4g .. a-4g+3 with a = jr + c - 3)
+//   mirrored half: step u reads byte jr - (2nt-1) - c + u
+// jr: tile-relative index of the frame's newest byte; c: the lane's skew.
+struct FrameCursor { const uint32_t* pf; const uint32_t* pb; int fsh, bsh; };
+__device__ __forceinline__ FrameCursor frame_cursor(const uint32_t* tw, int jr, int c, int nt) {
+    FrameCursor k;
+    const int a = jr + c - 3, b = jr - (2 * nt - 1) - c;
+    k.pf = tw + (a >> 2); k.fsh = (a & 3) * 8;
+    k.pb = tw + (b >> 2); k.bsh = (b & 3) * 8;
+    return k;
+}
+
 template <bool PAIR>
-__device__ __forceinline__ void lutfir_pair(const KParams& P, const LaneLut& L, const uint32_t* __restrict__ tw, int dW,
-                                            int jr, int c, uint32_t tp0, double& yA, double& yB) {
+__device__ __forceinline__ void lutfir_pair(const KParams& P, const LaneLut& L, const FrameCursor& K, int dW,
+                                            uint32_t tp0, double& yA, double& yB) {
     const int nt = P.nt;
-    // forward half: step u reads byte jr + c - u  (group g: bytes a-4g .. a-4g+3 with a = jr + c - 3)
-    const int a = jr + c - 3;
-    const uint32_t* pf = tw + (a >> 2);
-    const int fsh = (a & 3) * 8;
+    const uint32_t* pf = K.pf;
+    const uint32_t* pb = K.pb;
+    const int fsh = K.fsh, bsh = K.bsh;
+    const int c = L.c;
     uint32_t fhA = pf[1], fhB = PAIR ? pf[1 + dW] : 0u;
-    // mirrored half: step u reads byte jr - (2nt-1) - c + u
-    const int b = jr - (2 * nt - 1) - c;
-    const uint32_t* pb = tw + (b >> 2);
-    const int bsh = (b & 3) * 8;
     uint32_t blA = pb[0], blB = PAIR ? pb[dW] : 0u;
     // the words of the NEXT group are fetched one group ahead, so that a group never waits on its own tile loads
     uint32_t nfA = pf[0], nfB = PAIR ? pf[dW] : 0u, nbA = pb[1], nbB = PAIR ? pb[1 + dW] : 0u;
@@ -528,6 +518,7 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
     LaneLut LL;
     LL.rlo = (uint32_t)P.lut_row_bytes;
     LL.rhi = (uint32_t)P.lut_row_bytes << 16;
+    LL.c = c;
     LL.dz = 128 - P.zpad_bytes - (P.lut_st[r] & ~15) * 8;       // same bank pair, inside the zero region
 
     Emitter<WM, DITH> em; em.init();
@@ -564,6 +555,31 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
             const int items = P.C << P.tf_shift;                  // item = channel * TF + frame-in-tile
             const int bpo = P.bpo;
             em.set_job(*t.J);
+            if (t.nf == P.TF && P.TF >= 2 * nc) {
+                // Full tile whose channels split into whole passes of 2*nc frames: thread tid runs frames
+                // A = pass*2nc + tid and B = A + nc of every channel.  From one pass to the next both byte streams
+                // move by a whole number of words, so the cursor is set up once per tile and only advanced.
+                FrameCursor K = frame_cursor(reinterpret_cast<const uint32_t*>(tiles), (tid + 1) * bpo - 1 + t.jr_base, c, P.nt);
+                const int dW = (nc * bpo) >> 2, passW = (2 * nc * bpo) >> 2, chW = P.tile_stride >> 2;
+                const int npass = P.TF / (2 * nc);
+                for (int ch = 0; ch < P.C; ++ch) {
+                    FrameCursor Kp = K;
+                    for (int ps = 0, fl = tid; ps < npass; ++ps, fl += 2 * nc) {
+                        double yA, yB;
+                        lutfir_pair<true>(P, LL, Kp, dW, tp0, yA, yB);
+                        if (WM == 1) {                              // both dither / rounding chains side by side
+                            const int vA = em.quant(P, ch, t.f0 + fl, yA), vB = em.quant(P, ch, t.f0 + fl + nc, yB);
+                            em.put(P, *t.J, ostage, ch, t.f0 + fl, fl, vA);
+                            em.put(P, *t.J, ostage, ch, t.f0 + fl + nc, fl + nc, vB);
+                        } else {
+                            em.emit(P, *t.J, ostage, ch, t.f0 + fl, fl, yA);
+                            em.emit(P, *t.J, ostage, ch, t.f0 + fl + nc, fl + nc, yB);
+                        }
+                        Kp.pf += passW; Kp.pb += passW;
+                    }
+                    K.pf += chW; K.pb += chW;
+                }
+            } else
             // Passes over the tile's items.  While at least 2*nc items remain, every consumer thread runs two
             // frames in lockstep (A = base + tid, B = A + nc); a remainder of more than nc items is split into
             // two halves the same way; up to nc items run one frame per thread.
@@ -576,6 +592,7 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
                     const int ch = it >> P.tf_shift, fl = it & (P.TF - 1);
                     const uint32_t* tw = reinterpret_cast<const uint32_t*>(tiles + (size_t)ch * P.tile_stride);
                     const int jr = (fl + 1) * bpo - 1 + t.jr_base;
+                    const FrameCursor K = frame_cursor(tw, jr, c, P.nt);
                     if (pair) {
                         const int itB = it + ps;
                         const bool hasB = itB < items;
@@ -585,13 +602,20 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
                             // B's bytes sit a fixed, word-aligned distance from A's (ps and TF are multiples of 32)
                             const int dW = hasB ? ((chB - ch) * P.tile_stride + (flB - fl) * bpo) >> 2 : 0;
                             double yA, yB;
-                            lutfir_pair<true>(P, LL, tw, dW, jr, c, tp0, yA, yB);
-                            if (fl < t.nf) em.emit(P, *t.J, ostage, ch, t.f0 + fl, fl, yA);
-                            if (hasB && flB < t.nf) em.emit(P, *t.J, ostage, chB, t.f0 + flB, flB, yB);
+                            lutfir_pair<true>(P, LL, K, dW, tp0, yA, yB);
+                            const bool okA = fl < t.nf, okB = hasB && flB < t.nf;
+                            if (WM == 1 && okA && okB) {
+                                const int vA = em.quant(P, ch, t.f0 + fl, yA), vB = em.quant(P, chB, t.f0 + flB, yB);
+                                em.put(P, *t.J, ostage, ch, t.f0 + fl, fl, vA);
+                                em.put(P, *t.J, ostage, chB, t.f0 + flB, flB, vB);
+                            } else {
+                                if (okA) em.emit(P, *t.J, ostage, ch, t.f0 + fl, fl, yA);
+                                if (okB) em.emit(P, *t.J, ostage, chB, t.f0 + flB, flB, yB);
+                            }
                         }
                     } else if ((fl & ~31) < t.nf) {
                         double yA, yB;
-                        lutfir_pair<false>(P, LL, tw, 0, jr, c, tp0, yA, yB);
+                        lutfir_pair<false>(P, LL, K, 0, tp0, yA, yB);
                         if (fl < t.nf) em.emit(P, *t.J, ostage, ch, t.f0 + fl, fl, yA);
                     }
                 }
