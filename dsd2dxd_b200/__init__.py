@@ -165,6 +165,15 @@ def convert_host(cfg, raw, out=None):
     return out[: frames.value * cfg.channels * sb], frames.value, {"clipped_samples": clips.value, "peak_abs": peak.value}
 
 
+def check_level(cfg, raw):
+    """Peak level of a whole payload (Rdsd2Pcm::new_level_check + check_level, rd/lib.rs:124-182):
+    -> (peak_abs, peak_dbfs as float32)."""
+    raw = np.ascontiguousarray(raw, dtype=np.uint8)
+    peak, db = C.c_double(), C.c_float()
+    _capi.check(_capi.lib().d2p_check_level(C.byref(cfg), raw.ctypes.data, raw.size, C.byref(peak), C.byref(db)))
+    return peak.value, np.float32(db.value)
+
+
 class Batch:
     """Many payloads already resident in HBM, converted by one launch set (d2p_batch_*)."""
 

@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libdsd2pcm_b200.so")
 OK = 0
 ERR_INVALID_ARG, ERR_TAPS_NOT_FOUND, ERR_UNSUPPORTED_LM, ERR_BIT_DEPTH = 1, 2, 3, 4
 ERR_NO_DEVICE, ERR_CUDA, ERR_NOMEM, ERR_STATE, ERR_CAPACITY = 5, 6, 7, 8, 9
-OUT_INTERLEAVED_LE, OUT_INTERLEAVED_BE, OUT_PLANAR_32 = 0, 1, 2
+OUT_INTERLEAVED_LE, OUT_INTERLEAVED_BE, OUT_PLANAR_32, OUT_NONE = 0, 1, 2, 3
 
 
 class Config(C.Structure):
@@ -56,7 +56,7 @@ EXPORTS = [
     "d2p_abi_version", "d2p_strerror", "d2p_last_error", "d2p_device_count",
     "d2p_plan", "d2p_frames_for_bytes", "d2p_tap_table", "d2p_tap_table_count", "d2p_tap_table_name",
     "d2p_create", "d2p_destroy", "d2p_push", "d2p_finish", "d2p_frames_ready", "d2p_pull", "d2p_pull_f64", "d2p_stats",
-    "d2p_convert_host", "d2p_host_alloc", "d2p_host_free",
+    "d2p_convert_host", "d2p_check_level", "d2p_host_alloc", "d2p_host_free",
     "d2p_batch_create", "d2p_batch_destroy", "d2p_batch_run", "d2p_batch_convert_host", "d2p_batch_launches",
     "d2p_batch_stats", "d2p_total_frames", "d2p_block_range", "d2p_batch_run_blocks",
 ]
@@ -96,6 +96,7 @@ def lib():
     L.d2p_stats.argtypes = [vp, C.POINTER(C.c_int64), C.POINTER(C.c_double), C.POINTER(C.c_int64)]
     L.d2p_convert_host.argtypes = [cfgp, vp, C.c_size_t, vp, C.c_size_t, C.POINTER(C.c_uint64),
                                    C.POINTER(C.c_int64), C.POINTER(C.c_double)]
+    L.d2p_check_level.argtypes = [cfgp, vp, C.c_size_t, C.POINTER(C.c_double), C.POINTER(C.c_float)]
     L.d2p_host_alloc.restype = vp
     L.d2p_host_alloc.argtypes = [C.c_size_t]
     L.d2p_host_free.argtypes = [vp]

@@ -88,7 +88,7 @@ static void lutfir_geometry(const Plan& p, const LutLayout& L, int TF, int* tile
     const int C = p.cfg.channels;
     *tile_stride = (int)round16((size_t)TF * p.bpo + 2 * p.nt + 80) + 16;
     *in_buf = C * *tile_stride;
-    *ostage = p.cfg.out_format == D2P_OUT_PLANAR_32 ? 0 : (int)round16((size_t)TF * C * p.bps);
+    *ostage = (p.cfg.out_format == D2P_OUT_PLANAR_32 || p.cfg.out_format == D2P_OUT_NONE) ? 0 : (int)round16((size_t)TF * C * p.bps);
     *smem = (size_t)lutfir_zpad(p.nt, L.K) + (size_t)L.slots * 2048 + 2 * (size_t)*in_buf + 2 * (size_t)*ostage;
 }
 
@@ -120,7 +120,7 @@ static LmGeom lm_geometry(const Plan& p, const LmLut& ll, int TF, int NB) {
     }
     const long long bits = cnt1 * p.m1 / p.L + 64 + p.m1;
     g.tile_stride = (int)round16((size_t)(bits / 8) + 16) + 48;
-    const size_t ostage = p.cfg.out_format == D2P_OUT_PLANAR_32 ? 0 : round16((size_t)TF * C * p.bps);
+    const size_t ostage = (p.cfg.out_format == D2P_OUT_PLANAR_32 || p.cfg.out_format == D2P_OUT_NONE) ? 0 : round16((size_t)TF * C * p.bps);
     g.ostage = (int)ostage;
     g.smem = (size_t)ll.slots * 2048 + (size_t)NB * (g.s1_cap + g.s2_cap) * 8 + 2 * (size_t)C * g.tile_stride + 2 * ostage;
     return g;
@@ -718,6 +718,8 @@ const char* d2p_tap_table_name(int index) { const TapTable* t = table_at(index);
 int d2p_create(const d2p_config* cfg, d2p_ctx** out) {
     if (!cfg || !out) return set_err(D2P_ERR_INVALID_ARG, "null argument");
     *out = nullptr;
+    if (cfg->out_format == D2P_OUT_NONE)
+        return set_err(D2P_ERR_INVALID_ARG, "D2P_OUT_NONE (level check) is served by d2p_check_level / d2p_batch_*, not by a streaming context");
     DevicePlan* dp = nullptr;
     int st = build_device_plan(*cfg, &dp);
     if (st != D2P_OK) return st;
@@ -946,7 +948,8 @@ static int host_convert(const DevicePlan& dp, Launcher& launcher, HostPipe& pipe
     const long long tail_per = (long long)((nbytes - (size_t)groups * G) / c.channels);
     const long long total_q = groups * unit + tail_per;
     const long long total_frames = p.frames_for_bytes(total_q);
-    const size_t fb = (size_t)c.channels * p.bps;
+    const bool no_pcm = c.out_format == D2P_OUT_NONE;              // level check: nothing comes back
+    const size_t fb = no_pcm ? 0 : (size_t)c.channels * p.bps;
     *frames = 0;
     if ((size_t)total_frames * fb > out_cap_bytes) return set_err(D2P_ERR_CAPACITY, "output buffer too small");
     int rc = pipe.init();
@@ -985,8 +988,10 @@ static int host_convert(const DevicePlan& dp, Launcher& launcher, HostPipe& pipe
             j.out = pipe.d_out[s]; j.seed = c.dither_seed; j.total_q = total_q;
             if ((size_t)j.f_count * fb > pipe.out_cap) { rc = set_err(D2P_ERR_NOMEM, "internal: chunk output larger than staging buffer"); break; }
             if ((rc = launcher.run(dp, jobs, pipe.streams[s])) != D2P_OK) break;
-            e = cudaMemcpyAsync((uint8_t*)pcm + (size_t)f_done * fb, pipe.d_out[s], (size_t)j.f_count * fb, cudaMemcpyDeviceToHost, pipe.streams[s]);
-            if (e != cudaSuccess) { rc = cuda_err(e, "D2H"); break; }
+            if (!no_pcm) {
+                e = cudaMemcpyAsync((uint8_t*)pcm + (size_t)f_done * fb, pipe.d_out[s], (size_t)j.f_count * fb, cudaMemcpyDeviceToHost, pipe.streams[s]);
+                if (e != cudaSuccess) { rc = cuda_err(e, "D2H"); break; }
+            }
             f_done = f_new;
         }
         if (last) break;
@@ -1034,8 +1039,9 @@ void d2p_batch_destroy(d2p_batch* b) {
 
 int d2p_batch_convert_host(d2p_batch* b, const uint8_t* raw, size_t nbytes, void* pcm, size_t out_cap_bytes,
                            uint64_t* frames) {
-    if (!b || (!raw && nbytes) || !pcm || !frames) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    if (!b || (!raw && nbytes) || !frames) return set_err(D2P_ERR_INVALID_ARG, "null argument");
     const d2p_config& c = b->dp->plan.cfg;
+    if (!pcm && c.out_format != D2P_OUT_NONE) return set_err(D2P_ERR_INVALID_ARG, "null argument");
     if (c.out_format == D2P_OUT_PLANAR_32 || c.keep_f64)
         return set_err(D2P_ERR_INVALID_ARG, "host conversion produces interleaved packed PCM only");
     CK(cudaSetDevice(c.device));
@@ -1054,6 +1060,27 @@ int d2p_convert_host(const d2p_config* cfg, const uint8_t* raw, size_t nbytes, v
     return st;
 }
 
+// Rdsd2Pcm::new_level_check + check_level (rd/lib.rs:124-158, 171-182): 32-bit sink, no dither, 0 dB, equiripple.
+int d2p_check_level(const d2p_config* cfg, const uint8_t* raw, size_t nbytes, double* peak_abs, float* peak_dbfs) {
+    if (!cfg || (!raw && nbytes)) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    d2p_config c = *cfg;
+    c.bits = 32; c.dither = D2P_DITHER_NONE; c.level_db = 0.0; c.filter = D2P_FILTER_EQUIRIPPLE;
+    c.out_format = D2P_OUT_NONE; c.keep_f64 = 0; c.has_dither_scale = 0;
+    d2p_batch* b = nullptr;
+    int st = d2p_batch_create(&c, &b);
+    if (st != D2P_OK) return st;
+    uint64_t frames = 0;
+    double peak = 0.0;
+    st = d2p_batch_convert_host(b, raw, nbytes, nullptr, 0, &frames);
+    if (st == D2P_OK) st = d2p_batch_stats(b, nullptr, nullptr, &peak);
+    d2p_batch_destroy(b);
+    if (st != D2P_OK) return st;
+    if (peak_abs) *peak_abs = peak;
+    // process_levels :247-251
+    if (peak_dbfs) *peak_dbfs = peak <= 0.0 ? -INFINITY : (float)(20.0 * std::log10(peak));
+    return D2P_OK;
+}
+
 int d2p_batch_run(d2p_batch* b, d2p_job* jobs, int njobs, void* cuda_stream) {
     if (!b || (!jobs && njobs)) return set_err(D2P_ERR_INVALID_ARG, "null argument");
     const Plan& p = b->dp->plan;
@@ -1062,7 +1089,7 @@ int d2p_batch_run(d2p_batch* b, d2p_job* jobs, int njobs, void* cuda_stream) {
     const bool planar = c.in_layout == D2P_LAYOUT_PLANAR;
     const size_t G = group_bytes(c);
     const long long unit = planar ? (long long)c.block_size : 1;
-    const size_t fb = (size_t)c.channels * (c.out_format == D2P_OUT_PLANAR_32 ? 4 : p.bps);
+    const size_t fb = c.out_format == D2P_OUT_NONE ? 0 : (size_t)c.channels * (c.out_format == D2P_OUT_PLANAR_32 ? 4 : p.bps);
     std::vector<DevJob> dj((size_t)njobs);
     for (int i = 0; i < njobs; ++i) {
         d2p_job& u = jobs[i];
@@ -1116,7 +1143,7 @@ int d2p_batch_run_blocks(d2p_batch* b, const d2p_block_job* jobs, int njobs, voi
     const Plan& p = b->dp->plan;
     const d2p_config& c = p.cfg;
     CK(cudaSetDevice(c.device));
-    const size_t fb = (size_t)c.channels * (c.out_format == D2P_OUT_PLANAR_32 ? 4 : p.bps);
+    const size_t fb = c.out_format == D2P_OUT_NONE ? 0 : (size_t)c.channels * (c.out_format == D2P_OUT_PLANAR_32 ? 4 : p.bps);
     std::vector<DevJob> dj((size_t)njobs);
     for (int i = 0; i < njobs; ++i) {
         const d2p_block_job& u = jobs[i];

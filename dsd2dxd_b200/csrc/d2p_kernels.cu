@@ -256,6 +256,7 @@ struct Emitter {
         double s = __dmul_rn(y, P.scale);                       // scale_and_dither  rd/pcm_writer.rs:651
         const unsigned long long ab = (unsigned long long)__double_as_longlong(fabs(s));
         peakb = ab > peakb ? ab : peakb;
+        if (P.out_format == D2P_DEV_OUT_NONE) return;           // level check (process_levels): nothing is written
         if (P.has_ds) s = __dmul_rn(s, P.neg_scale);            // Dither::process_samp rd/dither.rs:86-95
         if (P.dither == 'T' || P.dither == 'R')
             s = __dadd_rn(s, dither_noise(P.dither, (unsigned long long)f, (uint32_t)ch, key));
@@ -522,7 +523,7 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
     LL.dz = 128 - P.zpad_bytes - (P.lut_st[r] & ~15) * 8;       // same bank pair, inside the zero region
 
     Emitter<WM, DITH> em; em.init();
-    const bool staged_out = P.out_format != D2P_DEV_OUT_PLANAR;
+    const bool staged_out = P.out_format == D2P_DEV_OUT_LE || P.out_format == D2P_DEV_OUT_BE;
     const size_t fb = (size_t)P.C * P.bps;
 
     unsigned int tile = blockIdx.x;
@@ -742,7 +743,7 @@ __global__ void __launch_bounds__(kLmThreads) lm_kernel(const __grid_constant__ 
     const int tid = threadIdx.x;
     const bool producer = tid >= kLmConsumers;
     const int ptid = tid - kLmConsumers, np = blockDim.x - kLmConsumers;
-    const bool staged_out = P.out_format != D2P_DEV_OUT_PLANAR;
+    const bool staged_out = P.out_format == D2P_DEV_OUT_LE || P.out_format == D2P_DEV_OUT_BE;
     const size_t fb = (size_t)P.C * P.bps;
 
     load_lut(lut, P.lut, P.lut_doubles);

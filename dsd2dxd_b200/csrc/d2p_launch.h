@@ -7,6 +7,7 @@
 #define D2P_DEV_OUT_LE 0
 #define D2P_DEV_OUT_BE 1
 #define D2P_DEV_OUT_PLANAR 2
+#define D2P_DEV_OUT_NONE 3
 
 namespace d2p {
 

@@ -139,7 +139,7 @@ int make_plan(const d2p_config& cfg, Plan* out, std::string* msg) {
     if (cfg.block_size == 0) return fail(D2P_ERR_INVALID_ARG, "block_size must be > 0");
     if (!(cfg.dither == 'T' || cfg.dither == 'R' || cfg.dither == 'F' || cfg.dither == 'X'))
         return fail(D2P_ERR_INVALID_ARG, "Invalid dither type; must be T, R, F, or X");
-    if (cfg.out_format < 0 || cfg.out_format > 2) return fail(D2P_ERR_INVALID_ARG, "invalid out_format");
+    if (cfg.out_format < 0 || cfg.out_format > 3) return fail(D2P_ERR_INVALID_ARG, "invalid out_format");
     if (!(cfg.bits == 16 || cfg.bits == 20 || cfg.bits == 24 || cfg.bits == 32))
         return fail(D2P_ERR_BIT_DEPTH, "Unsupported bit depth");
 

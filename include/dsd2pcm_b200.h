@@ -50,7 +50,9 @@ enum { D2P_LAYOUT_PLANAR = 'P', D2P_LAYOUT_INTERLEAVED = 'I' };
 enum {
     D2P_OUT_INTERLEAVED_LE = 0,   /* stdout / WAV payload: pack_int / pack_float  rd/pcm_writer.rs:365-396 */
     D2P_OUT_INTERLEAVED_BE = 1,   /* AIFF / AIFC payload  rd/audio_file.rs:257-275 */
-    D2P_OUT_PLANAR_32 = 2         /* AudioFile<i32|f32>.samples[channel][frame]  rd/pcm_writer.rs:411-421 (20-bit NOT shifted) */
+    D2P_OUT_PLANAR_32 = 2,        /* AudioFile<i32|f32>.samples[channel][frame]  rd/pcm_writer.rs:411-421 (20-bit NOT shifted) */
+    D2P_OUT_NONE = 3              /* level check: no PCM is written, only max |sample*scale| is kept
+                                     (PcmWriter::new_sink rd/pcm_writer.rs:151-182, process_levels rd/conversion_context.rs:209-256) */
 };
 
 /* Mirrors the parameters of Rdsd2Pcm::new (rd/lib.rs:75-91) that reach the hot path. */
@@ -134,6 +136,12 @@ int  d2p_stats(d2p_ctx* ctx, int64_t* clips, double* peak_abs, int64_t* clipped_
  * clips receives the plain count of clipped samples (the run-length statistic needs the streaming context). */
 int  d2p_convert_host(const d2p_config* cfg, const uint8_t* raw, size_t nbytes,
                       void* pcm, size_t out_cap_bytes, uint64_t* frames, int64_t* clips, double* peak_abs);
+/* Peak level of a whole payload in host memory: Rdsd2Pcm::new_level_check + check_level
+ * (rd/lib.rs:124-158, 171-182; process_levels rd/conversion_context.rs:209-256).  Like the reference it
+ * ignores cfg's bits / dither / level / out_format / filter (32-bit sink, no dither, 0 dB, equiripple filters):
+ * *peak_abs = max over all channels of |sample| * L,  *peak_dbfs = (f32)(20*log10(peak_abs)), -inf if silent.
+ * Runs the same kernels with the writer reduced to the level reduction; nothing is copied back but 8 bytes. */
+int  d2p_check_level(const d2p_config* cfg, const uint8_t* raw, size_t nbytes, double* peak_abs, float* peak_dbfs);
 /* Pinned host memory for the buffers above (plain malloc'ed memory also works, more slowly). */
 void* d2p_host_alloc(size_t nbytes);
 void  d2p_host_free(void* p);

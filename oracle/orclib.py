@@ -231,6 +231,16 @@ def convert(raw, want_f64=True, **kw):
     return r
 
 
+def check_level(raw, dsd_rate=1, out_rate=352800, channels=2, layout="P", lsb_first=True, block_size=4096):
+    """Rdsd2Pcm::new_level_check + process_levels (rd/lib.rs:124-158, rd/conversion_context.rs:209-256):
+    32-bit sink, no dither, 0 dB, equiripple; peak_abs = max |s| * scale_factor over every channel's samples,
+    peak_dbfs = (20 * log10(peak_abs)) as f32, -inf when peak_abs <= 0.  -> (peak_abs, np.float32 dBFS)."""
+    r = convert(raw, dsd_rate=dsd_rate, out_rate=out_rate, filt="E", bits=32, dither="X", level_db=0.0,
+                channels=channels, layout=layout, lsb_first=lsb_first, block_size=block_size)
+    peak = float(np.max(np.abs(r.f64) * r.scale)) if r.f64.size else 0.0
+    return peak, (np.float32(-np.inf) if peak <= 0.0 else np.float32(20.0 * np.log10(peak)))
+
+
 def bench(raw, nfiles, nthreads, **kw):
     cfg = make_config(**kw)
     raw = np.ascontiguousarray(raw, dtype=np.uint8)

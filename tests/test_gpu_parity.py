@@ -304,3 +304,39 @@ def test_fpd_dither_time_blocks_and_long_jump():
     got = np.concatenate([o.cpu().numpy()[:b.frame_count * 8] for b, o in zip(blocks, d_out)])
     assert np.array_equal(got, ref.pcm)
     batch.close()
+
+
+@pytest.mark.parametrize("dsd_rate,out_rate,channels,layout,lsb_first", [
+    (1, 352800, 2, "P", True), (4, 352800, 2, "P", True), (1, 96000, 2, "P", True), (4, 192000, 1, "P", True),
+    (8, 352800, 6, "I", False), (2, 88200, 2, "I", True)])
+def test_level_check_matches_process_levels(dsd_rate, out_rate, channels, layout, lsb_first):
+    """dsd_levels path: peak over all channels, no PCM written (D2P_OUT_NONE)."""
+    raw = rand_payload(900 + dsd_rate + channels, channels, 40)
+    raw[: raw.size // 3] = 0x69                                    # a quiet stretch in front, peaks later
+    cfg = d2p.make_config(dsd_rate=dsd_rate, out_rate=out_rate, channels=channels, layout=layout, lsb_first=lsb_first,
+                          bits=16, dither="T", level_db=-3.0, filt="E")     # all ignored, as in new_level_check
+    peak, db = d2p.check_level(cfg, raw)
+    ref_peak, ref_db = orclib.check_level(raw, dsd_rate=dsd_rate, out_rate=out_rate, channels=channels, layout=layout,
+                                          lsb_first=lsb_first)
+    assert peak == ref_peak
+    assert abs(float(db) - float(ref_db)) <= abs(float(np.spacing(ref_db)))
+
+
+def test_level_check_device_resident_batch_and_silence():
+    import torch
+    cfg = d2p.make_config(dsd_rate=1, out_rate=352800, bits=32, dither="X", out_format=_capi.OUT_NONE)
+    raws = [rand_payload(950 + i, 2, 12) for i in range(3)]
+    batch = d2p.Batch(cfg)
+    d_in = [torch.from_numpy(r).cuda() for r in raws]
+    jobs = batch.make_jobs(dict(d_in=t.data_ptr(), in_bytes=t.numel(), d_out=None, out_cap_bytes=0) for t in d_in)
+    frames = batch.run(jobs, torch.cuda.current_stream().cuda_stream)
+    st = batch.stats(torch.cuda.current_stream().cuda_stream)
+    batch.close()
+    refs = [orclib.check_level(r)[0] for r in raws]
+    assert frames == [d2p.frames_for_bytes(cfg, r.size // 2) for r in raws]
+    assert st["peak_abs"] == max(refs)
+    # nothing in, nothing out: -inf like process_levels
+    peak, db = d2p.check_level(cfg, np.zeros(0, dtype=np.uint8))
+    assert peak == 0.0 and np.isneginf(db)
+    with pytest.raises(_capi.D2PError):
+        d2p.Converter(cfg)                                         # the streaming context has no level-only mode
