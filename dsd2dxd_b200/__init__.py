@@ -230,3 +230,50 @@ class Batch:
         clipped, peak = C.c_int64(), C.c_double()
         _capi.check(_capi.lib().d2p_batch_stats(self._h, C.c_void_p(stream), C.byref(clipped), C.byref(peak)))
         return {"clipped_samples": clipped.value, "peak_abs": peak.value}
+
+
+# ---- container front / back end (include/dsd2pcm_b200_files.h) ------------------------------------------
+def _info_dict(ci):
+    return {k: getattr(ci, k) for k, _ in _capi.ContainerInfo._fields_}
+
+
+def container_parse(data, file_bytes=None):
+    """Headers of a DSF / DSDIFF file held in memory -> dict (d2p_container_parse)."""
+    data = np.ascontiguousarray(np.frombuffer(bytes(data), dtype=np.uint8))
+    ci = _capi.ContainerInfo()
+    _capi.check(_capi.lib().d2p_container_parse(data.ctypes.data, data.size, data.size if file_bytes is None else file_bytes,
+                                                C.byref(ci)))
+    return _info_dict(ci)
+
+
+def container_open(path):
+    ci = _capi.ContainerInfo()
+    _capi.check(_capi.lib().d2p_container_open(str(path).encode(), C.byref(ci)))
+    return _info_dict(ci)
+
+
+def pcm_header(container, bits, channels, rate, frames):
+    """Header bytes of a WAV ('W') / AIFF ('A') / AIFC ('C') file (d2p_pcm_header); b'' if unsupported."""
+    n = _capi.lib().d2p_pcm_header(ord(container), bits, channels, rate, frames, None, 0)
+    buf = np.zeros(max(n, 1), dtype=np.uint8)
+    _capi.lib().d2p_pcm_header(ord(container), bits, channels, rate, frames, buf.ctypes.data, buf.size)
+    return buf[:n].tobytes()
+
+
+def write_pcm_file(path, container, bits, channels, rate, payload, frames):
+    payload = np.ascontiguousarray(payload, dtype=np.uint8)
+    _capi.check(_capi.lib().d2p_write_pcm_file(str(path).encode(), ord(container), bits, channels, rate,
+                                               payload.ctypes.data, frames))
+
+
+def convert_file(in_path, out_path, out_rate=352800, filt="E", bits=24, dither="X", level_db=0.0, container="W",
+                 dither_seed=0, device=0, dsf_stop_at_sample_count=False, raw_channels=2, raw_layout="P",
+                 raw_lsb_first=True, raw_dsd_rate=1, raw_block_size=4096):
+    """One DSF / DSDIFF / raw DSD file -> one PCM file on the GPU (d2p_convert_file).  Returns a dict."""
+    opt = _capi.FileOptions(out_rate, ord(filt), bits, ord(dither), level_db, ord(container), dither_seed, device,
+                            1 if dsf_stop_at_sample_count else 0, raw_channels, ord(raw_layout),
+                            1 if raw_lsb_first else 0, raw_dsd_rate, raw_block_size)
+    res = _capi.FileResult()
+    _capi.check(_capi.lib().d2p_convert_file(C.byref(opt), str(in_path).encode(), str(out_path).encode(), C.byref(res)))
+    return {"in": _info_dict(res.info), "frames": int(res.frames), "out_bytes": int(res.out_bytes),
+            "clipped_samples": int(res.clipped_samples), "peak_abs": float(res.peak_abs)}

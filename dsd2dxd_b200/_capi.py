@@ -51,7 +51,31 @@ class BlockJob(C.Structure):
     ]
 
 
-# every symbol include/dsd2pcm_b200.h declares
+class ContainerInfo(C.Structure):
+    _fields_ = [
+        ("format", C.c_int32), ("channels", C.c_int32), ("dsd_rate", C.c_int32), ("sample_rate", C.c_uint32),
+        ("in_layout", C.c_int32), ("lsb_first", C.c_int32), ("block_size", C.c_uint32),
+        ("data_offset", C.c_uint64), ("data_bytes", C.c_uint64), ("sample_count", C.c_uint64),
+        ("id3_offset", C.c_uint64), ("id3_bytes", C.c_uint64),
+    ]
+
+
+class FileOptions(C.Structure):
+    _fields_ = [
+        ("out_rate", C.c_uint32), ("filter", C.c_int32), ("bits", C.c_int32), ("dither", C.c_int32),
+        ("level_db", C.c_double), ("out_container", C.c_int32), ("dither_seed", C.c_uint64), ("device", C.c_int32),
+        ("dsf_stop_at_sample_count", C.c_int32),
+        ("raw_channels", C.c_int32), ("raw_layout", C.c_int32), ("raw_lsb_first", C.c_int32), ("raw_dsd_rate", C.c_int32),
+        ("raw_block_size", C.c_uint32),
+    ]
+
+
+class FileResult(C.Structure):
+    _fields_ = [("info", ContainerInfo), ("frames", C.c_uint64), ("out_bytes", C.c_uint64),
+                ("clipped_samples", C.c_int64), ("peak_abs", C.c_double)]
+
+
+# every symbol include/dsd2pcm_b200.h and include/dsd2pcm_b200_files.h declare
 EXPORTS = [
     "d2p_abi_version", "d2p_strerror", "d2p_last_error", "d2p_device_count",
     "d2p_plan", "d2p_frames_for_bytes", "d2p_tap_table", "d2p_tap_table_count", "d2p_tap_table_name",
@@ -59,6 +83,7 @@ EXPORTS = [
     "d2p_convert_host", "d2p_check_level", "d2p_host_alloc", "d2p_host_free",
     "d2p_batch_create", "d2p_batch_destroy", "d2p_batch_run", "d2p_batch_convert_host", "d2p_batch_launches",
     "d2p_batch_stats", "d2p_total_frames", "d2p_block_range", "d2p_batch_run_blocks",
+    "d2p_container_parse", "d2p_container_open", "d2p_pcm_header", "d2p_write_pcm_file", "d2p_convert_file",
 ]
 
 _lib = None
@@ -113,6 +138,13 @@ def lib():
     L.d2p_total_frames.argtypes = [cfgp, C.c_uint64]
     L.d2p_block_range.argtypes = [cfgp, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.d2p_batch_run_blocks.argtypes = [vp, C.POINTER(BlockJob), C.c_int, vp]
+    cip = C.POINTER(ContainerInfo)
+    L.d2p_container_parse.argtypes = [vp, C.c_size_t, C.c_uint64, cip]
+    L.d2p_container_open.argtypes = [C.c_char_p, cip]
+    L.d2p_pcm_header.restype = C.c_size_t
+    L.d2p_pcm_header.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint64, vp, C.c_size_t]
+    L.d2p_write_pcm_file.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_uint32, vp, C.c_uint64]
+    L.d2p_convert_file.argtypes = [C.POINTER(FileOptions), C.c_char_p, C.c_char_p, C.POINTER(FileResult)]
     _lib = L
     return L
 

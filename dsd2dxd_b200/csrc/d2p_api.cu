@@ -35,6 +35,7 @@ static int cuda_err(cudaError_t e, const char* what) {
     std::snprintf(buf, sizeof buf, "%s: %s", what, cudaGetErrorString(e));
     return set_err((e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) ? D2P_ERR_NO_DEVICE : D2P_ERR_CUDA, buf);
 }
+int api_set_error(int st, const char* msg) { return set_err(st, msg ? msg : ""); }   // for d2p_files.cpp
 #define CK(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return cuda_err(e__, #call); } while (0)
 
 static const unsigned int kEventCap = 1u << 16;

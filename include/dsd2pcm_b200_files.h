@@ -1,0 +1,95 @@
+/*
+ * dsd2pcm_b200_files.h -- container front end and back end around the conversion core
+ * (SURVEY.md 8(f) rows 2 and 3): DSF / DSDIFF / raw DSD readers, WAV / AIFF / AIFC writers, and a
+ * whole-file conversion call that strings them around d2p_convert_host().
+ *
+ * Reference interfaces these entry points stand in for:
+ *   reader   DsdReader::from_container / DsdReader::new   (crate dsd-reader 0.2.0 -- source NOT in the
+ *            reference mount; call sites rd/lib.rs:92-99, 171-183).  Re-created from the
+ *            DSF (Sony "DSF File Format Specification" 1.01) and DSDIFF 1.5 layouts and the contract
+ *            the call sites imply (per-channel block size, channel count, DSD rate, bit order, ID3 blob).
+ *   writers  AudioFile::save_wave_file / save_aiff_file / save_aifc_file / encode_extended
+ *            rd/audio_file.rs:93-207, 209-292, 294-452, 576-621   (byte for byte, quirks included)
+ *   driver   Rdsd2Pcm::from_container + do_conversion + PcmWriter::save_file
+ *            rd/lib.rs:171-182, 275-281, rd/pcm_writer.rs:300-318
+ * (rd/ = src/rdsd2pcm/src/ of the reference.)  Host-side byte formatting only: every sample still
+ * comes from the CUDA kernels; the payload reaches the file in the byte order the kernel packed it.
+ * FLAC encoding, ID3 -> tag copy and output naming stay out of scope.
+ */
+#ifndef DSD2PCM_B200_FILES_H
+#define DSD2PCM_B200_FILES_H
+
+#include "dsd2pcm_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { D2P_CONTAINER_DSF = 'S', D2P_CONTAINER_DFF = 'F', D2P_CONTAINER_RAW = 'R' };
+/* Output containers: the reference CLI's -o letters that carry PCM (src/main.rs:196-204) */
+enum { D2P_FILE_WAV = 'W', D2P_FILE_AIFF = 'A', D2P_FILE_AIFC = 'C', D2P_FILE_RAW = 'S' /* stdout-style headerless LE */ };
+
+typedef struct d2p_container_info {
+    int32_t  format;          /* D2P_CONTAINER_* */
+    int32_t  channels;
+    int32_t  dsd_rate;        /* sample_rate / 2 822 400: 1, 2, 4, 8 (0 if not a DSD64 multiple) */
+    uint32_t sample_rate;     /* Hz, as stored */
+    int32_t  in_layout;       /* D2P_LAYOUT_PLANAR (DSF) / D2P_LAYOUT_INTERLEAVED (DFF) */
+    int32_t  lsb_first;       /* DSF bits_per_sample == 1 -> 1; DSF 8 and DFF -> 0 */
+    uint32_t block_size;      /* bytes per channel per block (DSF: 4096; DFF: 1) */
+    uint64_t data_offset;     /* file offset of the first payload byte */
+    uint64_t data_bytes;      /* payload bytes present in the file (all channels, whole block groups for DSF) */
+    uint64_t sample_count;    /* DSF: samples per channel from the fmt chunk; DFF: data_bytes * 8 / channels */
+    uint64_t id3_offset;      /* ID3v2 blob (DSF metadata pointer / DFF "ID3 " chunk), 0 if none */
+    uint64_t id3_bytes;       /* clipped to the file size (the reference tolerates truncated tags) */
+} d2p_container_info;
+
+/* Parse the headers of a DSF or DSDIFF file held in memory (`bytes` = what is available of the file's
+ * beginning, `file_bytes` = the real file length; chunk sizes that point past it are clipped, as the
+ * wrong FRM8 size of id3_test/dff/1kHz_stereo_i.dff demands).  Returns D2P_ERR_INVALID_ARG for
+ * anything that is not DSD in a DSF / DSDIFF container (compressed DST included). */
+int d2p_container_parse(const uint8_t* bytes, size_t nbytes, uint64_t file_bytes, d2p_container_info* info);
+/* The same from a path (reads the header region and, for DSDIFF, walks the chunk list). */
+int d2p_container_open(const char* path, d2p_container_info* info);
+
+/* Header of a PCM file whose payload is `frames` frames of packed interleaved samples
+ * (WAV: little-endian, AIFF / AIFC: big-endian; 20-bit samples left-aligned in 3 bytes).
+ * Writes at most cap bytes to `out` and returns the header length (0 = unsupported combination:
+ * AIFF with 32-bit float, bits outside 16/20/24/32).  AIFC places a FLLR chunk so that the sample
+ * data starts on a 4096-byte boundary (rd/audio_file.rs:331-343); the header can therefore be 4 KiB. */
+size_t d2p_pcm_header(int container, int bits, int channels, uint32_t rate, uint64_t frames, uint8_t* out, size_t cap);
+/* header + payload -> file */
+int d2p_write_pcm_file(const char* path, int container, int bits, int channels, uint32_t rate,
+                       const void* payload, uint64_t frames);
+
+typedef struct d2p_file_options {
+    uint32_t out_rate;        /* -r */
+    int32_t  filter;          /* -t  D2P_FILTER_* */
+    int32_t  bits;            /* -b  16 / 20 / 24 / 32 */
+    int32_t  dither;          /* -d  D2P_DITHER_* */
+    double   level_db;        /* -l */
+    int32_t  out_container;   /* -o  D2P_FILE_* */
+    uint64_t dither_seed;
+    int32_t  device;
+    int32_t  dsf_stop_at_sample_count;   /* 0: convert every whole block of the data chunk; 1: stop at fmt.sample_count */
+    /* raw input (.dsd / anything that is not DSF or DSDIFF): the CLI's -c -f -e -s -i */
+    int32_t  raw_channels, raw_layout, raw_lsb_first, raw_dsd_rate;
+    uint32_t raw_block_size;
+} d2p_file_options;
+
+typedef struct d2p_file_result {
+    d2p_container_info in;
+    uint64_t frames;          /* per channel */
+    uint64_t out_bytes;       /* size of the file written */
+    int64_t  clipped_samples;
+    double   peak_abs;
+} d2p_file_result;
+
+/* One input file -> one PCM file: parse the container, stream the payload through the GPU
+ * (d2p_convert_host: pinned staging, H2D / kernel / D2H overlapped), write header + payload. */
+int d2p_convert_file(const d2p_file_options* opt, const char* in_path, const char* out_path, d2p_file_result* res);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DSD2PCM_B200_FILES_H */

@@ -1,4 +1,4 @@
-"""The C-ABI library loads on a CPU-only box and exports every symbol include/dsd2pcm_b200.h declares.
+"""The C-ABI library loads on a CPU-only box and exports every symbol include/*.h declare.
 Host-only entries (planning, tap tables, error strings) are exercised; compute entries must fail
 loudly with D2P_ERR_NO_DEVICE when no GPU is present (there is no CPU fallback)."""
 import ctypes as C
@@ -15,7 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def declared_symbols():
-    text = open(os.path.join(ROOT, "include", "dsd2pcm_b200.h")).read()
+    text = "".join(open(os.path.join(ROOT, "include", h)).read() for h in ("dsd2pcm_b200.h", "dsd2pcm_b200_files.h"))
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     return sorted(set(re.findall(r"\b(d2p_[a-z0-9_]+)\s*\(", text)))
 
