@@ -175,7 +175,8 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
         if (p.gmax > 5 || p.ring_cap != 32 || (int)p.L > kMaxPhasesDev)
             return set_err(D2P_ERR_INVALID_ARG, "internal: stage-1 filter outside the kernel's group / ring assumptions");
         const LmLut ll = lm_lut_layout(p);
-        const int nhw = kLmConsumers / 16;
+        const int cons = p.nstages == 3 ? kLmConsumers : kLmConsumersSmall;   // see d2p_launch.h
+        const int nhw = cons / 16;
         { int a = p.m1 % (int)p.L, b = (int)p.L; while (b) { const int t = a % b; a = b; b = t; }
           if (a != 1) return set_err(D2P_ERR_INVALID_ARG, "internal: m1 and L are not coprime"); }
         if (((long long)p.m1 * ll.A * nhw) % p.L != 0 || (ll.cyc == 2 && ((long long)p.m1 * ll.A * 2) % p.L != 0))
@@ -189,7 +190,9 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
                 if (C % nb != 0 && nb != C) continue;
                 const LmGeom g = lm_geometry(p, ll, tf, nb);
                 if (g.smem > budget) continue;
-                const double busy = std::min(1.0, (double)nb * tf / 512.0);   // stages 2/3: >= 16 warps of outputs
+                // stages 2/3 hand one output to each consumer thread per round: count the idle threads of the last round
+                const double items = (double)nb * tf;
+                const double busy = items / (std::ceil(items / cons) * cons);
                 const double score = busy * tf / (tf + halo);
                 if (score > best_score * 1.0001) { best_score = score; best_tf = tf; best_nb = nb; }
             }
@@ -202,7 +205,8 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
         k.lm_base_hi = p.stage1_nhi(0);
         k.lm_step_t = (long long)p.m1 * ll.A * nhw / p.L;
         k.ostage_bytes = g.ostage;
-        dp->threads = kLmThreads;
+        dp->threads = cons + kLmProducers;
+        k.lm_cons = cons;
         k.sigma2 = (p.D2 - p.h2 % p.D2) % p.D2;
         k.sigma3 = p.nstages == 3 ? (p.D3 - p.h3 % p.D3) % p.D3 : 0;
         k.inv_d2 = (65536 + p.D2 - 1) / p.D2;

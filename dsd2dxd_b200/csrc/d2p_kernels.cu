@@ -659,6 +659,19 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
 // e = T0 - k and the back sample e = k: the front address walks one row down per tap, the back address one row
 // up.  sigma = -h (mod D) makes both walkers wrap at the same taps (rows rf and D-1-rf), so the taps split into
 // a few straight runs.  `col` already points at this output's column.  All bookkeeping is warp-uniform.
+// N taps of one straight run, all operand loads ahead of the adds: the loads of a run are independent of the
+// accumulator chain, so the compiler may issue them back to back (software pipelining by full unrolling).
+template <int N>
+__device__ __forceinline__ double fir_run(const double* __restrict__ taps, const double*& pf, const double*& pb, int pitch,
+                                          double total) {
+    double f[N], b[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) { f[i] = *pf; b[i] = *pb; pf -= pitch; pb += pitch; }
+#pragma unroll
+    for (int i = 0; i < N; ++i) total = __dadd_rn(total, __dmul_rn(taps[i], __dadd_rn(f[i], b[i])));
+    return total;
+}
+
 __device__ __forceinline__ double fir_sym_t(const double* __restrict__ taps, const double* __restrict__ col, int h, int D,
                                             int pitch, int sigma) {
     const int ef = 2 * h - 1 + sigma;                               // front element of tap 0 (T0 = 2h-1), shifted
@@ -671,11 +684,10 @@ __device__ __forceinline__ double fir_sym_t(const double* __restrict__ taps, con
     while (k < h) {
         int run = rf + 1;                                           // taps until both walkers leave the tile rows
         if (h - k < run) run = h - k;
-#pragma unroll 4
-        for (int i = 0; i < run; ++i) {
-            total = __dadd_rn(total, __dmul_rn(taps[k + i], __dadd_rn(*pf, *pb)));
-            pf -= pitch; pb += pitch;
-        }
+        int i = 0;
+        for (; i + 7 <= run; i += 7) total = fir_run<7>(taps + k + i, pf, pb, pitch, total);   // D is 3, 7, 14 or 28
+        for (; i + 3 <= run; i += 3) total = fir_run<3>(taps + k + i, pf, pb, pitch, total);
+        for (; i < run; ++i) total = fir_run<1>(taps + k + i, pf, pb, pitch, total);
         k += run;
         rf = D - 1; pf += wrap; pb -= wrap;                         // front: previous column, top row; back: next column, row 0
     }
@@ -725,12 +737,13 @@ __device__ __forceinline__ void lm_tile_header(const KParams& P, unsigned int ti
     H.dA = (int)(tA - 31 - 8 * s_lo);                              // tile-relative bit of output nA's oldest window bit
 }
 
-__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" :: "n"(kLmConsumers) : "memory"); }
+template <int NCONS>
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" :: "n"(NCONS) : "memory"); }
 
 // kLmConsumers consumer threads run the stages; kLmProducers extra threads stage the next tile's input from
 // HBM and copy the previous tile's packed PCM out (double-buffered), so no consumer ever waits on HBM.
-template <int GMAX>
-__global__ void __launch_bounds__(kLmThreads) lm_kernel(const __grid_constant__ KParams P) {
+template <int GMAX, int NCONS>
+__global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __grid_constant__ KParams P) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ LmTile hdr[2];
     double* lut = reinterpret_cast<double*>(smem);
@@ -741,15 +754,15 @@ __global__ void __launch_bounds__(kLmThreads) lm_kernel(const __grid_constant__ 
     unsigned char* ostage0 = tiles0 + 2 * tiles_bytes;
 
     const int tid = threadIdx.x;
-    const bool producer = tid >= kLmConsumers;
-    const int ptid = tid - kLmConsumers, np = blockDim.x - kLmConsumers;
+    const bool producer = tid >= NCONS;
+    const int ptid = tid - NCONS, np = blockDim.x - NCONS;
     const bool staged_out = P.out_format == D2P_DEV_OUT_LE || P.out_format == D2P_DEV_OUT_BE;
     const size_t fb = (size_t)P.C * P.bps;
 
     load_lut(lut, P.lut, P.lut_doubles);
     Emitter<0, 0> em; em.init();
 
-    const int u = tid & 15, hw = tid >> 4, nhw = kLmConsumers >> 4;
+    const int u = tid & 15, hw = tid >> 4, nhw = NCONS >> 4;
     const int A = P.lmA;
     // block of this lane: u, or u + A for odd half-warps when the phase pattern alternates (lm_cyc == 2)
     const uint32_t tpl = (uint32_t)__cvta_generic_to_shared(lut) + (uint32_t)(P.lmGp * (u + A * (hw & (P.lm_cyc - 1))) * 8);
@@ -809,6 +822,22 @@ __global__ void __launch_bounds__(kLmThreads) lm_kernel(const __grid_constant__ 
                     for (int sl = 0; sl < nbc; ++sl) {
                         const uint32_t* tw = reinterpret_cast<const uint32_t*>(tiles + (size_t)(cb + sl) * P.tile_stride);
                         double* pd = s1 + (size_t)sl * P.s1_cap + p0 * P.pitch2 + q0;
+                        if (step_ph == 0 && relz <= rel0) {
+                            // the usual case: a round advances a whole number of stage-2 periods (the lane's row of the
+                            // phase-major tile never changes) and every output of the tile exists
+#pragma unroll 2
+                            for (int rel = rel0, d = d0; rel <= last_rel; rel += step_n, d += step_t, pd += step_q) {
+                                const int w = d >> 5;
+                                const uint32_t z = __brev(__funnelshift_r(tw[w], tw[w + 1], d & 31));   // bit j = x[t-j]
+                                double y = lds_f64<0>(__dp2a_lo(rlo, z, tpl));
+                                if (GMAX > 1) y = __dadd_rn(y, lds_f64<8>(__dp2a_lo(rhi, z, tpl)));
+                                if (GMAX > 2) y = __dadd_rn(y, lds_f64<16>(__dp2a_hi(rlo, z, tpl)));
+                                if (GMAX > 3) y = __dadd_rn(y, lds_f64<24>(__dp2a_hi(rhi, z, tpl)));
+                                if (GMAX > 4) y = __dadd_rn(y, lds_f64<32>(__dp2a_lo(rlo, z, tpl)));   // 8g mod 32: byte 0 again
+                                *pd = y;
+                            }
+                            continue;
+                        }
                         int ph = p0, d = d0;
                         for (int rel = rel0; rel <= last_rel; rel += step_n, d += step_t) {
                             double y = 0.0;                         // pre-stream stage-1 samples are 0.0 (ring zero-init)
@@ -827,9 +856,9 @@ __global__ void __launch_bounds__(kLmThreads) lm_kernel(const __grid_constant__ 
                         }
                     }
                 }
-                consumer_sync();
+                consumer_sync<NCONS>();
                 // ---- stage 2 (A9) ----
-                for (int item = tid; item < nbc * cnt2; item += kLmConsumers) {
+                for (int item = tid; item < nbc * cnt2; item += NCONS) {
                     int sl = 0, idx = item;
                     while (idx >= cnt2) { idx -= cnt2; ++sl; }
                     double tot = 0.0;
@@ -844,15 +873,15 @@ __global__ void __launch_bounds__(kLmThreads) lm_kernel(const __grid_constant__ 
                 }
                 // ---- stage 3 ----
                 if (P.nstages == 3) {
-                    consumer_sync();
-                    for (int item = tid; item < nbc * nf; item += kLmConsumers) {
+                    consumer_sync<NCONS>();
+                    for (int item = tid; item < nbc * nf; item += NCONS) {
                         int sl = 0, idx = item;
                         while (idx >= nf) { idx -= nf; ++sl; }
                         const double y = fir_sym_t(P.c3, s2 + (size_t)sl * P.s2_cap + idx, P.h3, P.D3, P.pitch3, P.sigma3);
                         em.emit(P, J, ostage, cb + sl, f0 + idx, idx, y);
                     }
                 }
-                if (cb + P.NB < P.C) consumer_sync();               // s1/s2 are reused by the next channel group
+                if (cb + P.NB < P.C) consumer_sync<NCONS>();               // s1/s2 are reused by the next channel group
             }
         }
         __syncthreads();
@@ -937,11 +966,16 @@ const char* kernel_name(bool lm) { return lm ? "d2p::lm_kernel" : "d2p::lutfir_k
 // variant: 0 = lm_kernel, 1 = lutfir generic writer, 2/3/4 = lutfir fast 3-byte-LE writer with dither X/T/R
 static const void* kernel_fn(int variant) {
     switch (variant) {
-    case 0: case 15: return (const void*)lm_kernel<5>;
-    case 11: return (const void*)lm_kernel<1>;
-    case 12: return (const void*)lm_kernel<2>;
-    case 13: return (const void*)lm_kernel<3>;
-    case 14: return (const void*)lm_kernel<4>;
+    case 0: case 15: return (const void*)lm_kernel<5, kLmConsumersSmall>;
+    case 11: return (const void*)lm_kernel<1, kLmConsumersSmall>;
+    case 12: return (const void*)lm_kernel<2, kLmConsumersSmall>;
+    case 13: return (const void*)lm_kernel<3, kLmConsumersSmall>;
+    case 14: return (const void*)lm_kernel<4, kLmConsumersSmall>;
+    case 21: return (const void*)lm_kernel<1, kLmConsumers>;
+    case 22: return (const void*)lm_kernel<2, kLmConsumers>;
+    case 23: return (const void*)lm_kernel<3, kLmConsumers>;
+    case 24: return (const void*)lm_kernel<4, kLmConsumers>;
+    case 25: return (const void*)lm_kernel<5, kLmConsumers>;
     case 2: return (const void*)lutfir_kernel<1, 0>;
     case 3: return (const void*)lutfir_kernel<1, 'T'>;
     case 4: return (const void*)lutfir_kernel<1, 'R'>;
@@ -950,13 +984,13 @@ static const void* kernel_fn(int variant) {
 }
 
 int kernel_variant(const KParams& P, bool lm, bool fast_writer_ok) {
-    if (lm) return 10 + (P.gmax < 1 ? 1 : (P.gmax > 5 ? 5 : P.gmax));
+    if (lm) return (P.lm_cons == kLmConsumers ? 20 : 10) + (P.gmax < 1 ? 1 : (P.gmax > 5 ? 5 : P.gmax));
     if (!fast_writer_ok) return 1;
     return P.dither == 'T' ? 3 : (P.dither == 'R' ? 4 : 2);
 }
 
 static cudaError_t ensure_smem_attr(int variant) {
-    static bool attr_done[16][64] = {};
+    static bool attr_done[32][64] = {};
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
@@ -970,7 +1004,7 @@ static cudaError_t ensure_smem_attr(int variant) {
 }
 
 int max_ctas_per_sm(bool lm, int threads, size_t smem) {
-    const int variant = lm ? 0 : 1;
+    const int variant = lm ? (threads > kLmConsumersSmall + kLmProducers ? 25 : 15) : 1;
     if (ensure_smem_attr(variant) != cudaSuccess) return 0;
     int n = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel_fn(variant), threads, smem) != cudaSuccess) { cudaGetLastError(); return 0; }

@@ -15,7 +15,13 @@ static const int kMaxThreads = 512;          // CTA size of lm_kernel; consumer 
 static const int kLutfirProducers = 128;     // extra threads of lutfir_kernel that stage tiles and copy results out
 static const int kLutfirThreads = kMaxThreads + kLutfirProducers;
 static const int kLmProducers = 64;          // extra threads of lm_kernel (same role)
-static const int kLmConsumers = 896;         // consumer threads of lm_kernel (stage work)
+// Consumer threads of lm_kernel: two instantiations.  448 = 28 half-warps: with 512 threads per CTA each thread may keep
+// 128 registers, which the unrolled FIR runs of the long two-stage chains use to put all loads of a run ahead of the
+// adds.  896 = 56 half-warps (64 registers): the three-stage chains, whose short runs (D3 = 3) gain nothing from
+// registers, prefer the extra warps.  Both make one stage-1 round (A * half-warps outputs) a multiple of every stage-2
+// decimation in use (7, 14, 28), so a lane's row in the phase-major tile never changes.
+static const int kLmConsumersSmall = 448;
+static const int kLmConsumers = 896;
 static const int kLmThreads = kLmConsumers + kLmProducers;
 static const int kLutPad = 128;              // legacy pad constant (lm_kernel does not use it)
 static const int kMaxSmem = 227 * 1024;      // opt-in dynamic shared memory per CTA on sm_100a
