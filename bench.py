@@ -223,6 +223,21 @@ def main():
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     assert got == frames
+    # what the same bytes cost as bare copies (H2D of one file's payload and D2H of its PCM at once, pinned memory, two
+    # streams): the ceiling of any host-buffer path on this box, reported beside e2e
+    th_in, th_out = torch.from_numpy(h_in.array), torch.from_numpy(h_out.array)
+    cs = [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)]
+    copy_s = []
+    for _ in range(3):
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        with torch.cuda.stream(cs[0]):
+            d_in[0].copy_(th_in, non_blocking=True)
+        with torch.cuda.stream(cs[1]):
+            th_out.copy_(d_out[0][:out_bytes], non_blocking=True)
+        torch.cuda.synchronize()
+        copy_s.append(time.perf_counter() - t1)
+    copy_file_s = min(copy_s)
     # the host path must give the same bytes as the device-resident path
     same = bool(np.array_equal(h_out.array[:out_bytes], d_out[0][:out_bytes].cpu().numpy())) if args.dither == "X" else None
     clocks = sampler.stop()
@@ -265,7 +280,11 @@ def main():
             "realtime_factor": value / (2 * 11289600.0),
             "e2e": {"value": e2e_value, "unit": "DSD samples/s", "h2d_bytes_per_step": nf * in_bytes,
                     "d2h_bytes_per_step": nf * out_bytes, "files_per_step": nf, "timer": "wall clock around the synchronous host call",
-                    "realtime_factor": e2e_value / (2 * 11289600.0), "matches_device_path": same},
+                    "realtime_factor": e2e_value / (2 * 11289600.0), "matches_device_path": same,
+                    "copies_alone": {"what": "bare pinned H2D of one file's payload + D2H of its PCM on two streams, rank 0",
+                                     "seconds_per_file": copy_file_s, "h2d_gbs": in_bytes / copy_file_s / 1e9,
+                                     "d2h_gbs": out_bytes / copy_file_s / 1e9,
+                                     "e2e_over_copy_time": (e2e_s / (nf * args.steps)) / copy_file_s}},
             "gpu_launches": int(launches),
             "kernel": "d2p::lutfir_kernel", "kernel_ms": kernel_ms,
             "roofline": {"bound": "hbm", "achieved": alg_bytes / (kernel_ms / 1e3) / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
