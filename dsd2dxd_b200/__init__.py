@@ -99,6 +99,12 @@ class Converter:
         raw = np.ascontiguousarray(raw, dtype=np.uint8)
         _capi.check(_capi.lib().d2p_push(self._h, raw.ctypes.data, raw.size))
 
+    def flush(self):
+        _capi.check(_capi.lib().d2p_flush(self._h))
+
+    def set_push_threshold(self, nbytes):
+        _capi.check(_capi.lib().d2p_set_push_threshold(self._h, nbytes))
+
     def finish(self):
         _capi.check(_capi.lib().d2p_finish(self._h))
 

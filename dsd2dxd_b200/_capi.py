@@ -79,7 +79,7 @@ class FileResult(C.Structure):
 EXPORTS = [
     "d2p_abi_version", "d2p_strerror", "d2p_last_error", "d2p_device_count",
     "d2p_plan", "d2p_frames_for_bytes", "d2p_tap_table", "d2p_tap_table_count", "d2p_tap_table_name",
-    "d2p_create", "d2p_destroy", "d2p_push", "d2p_finish", "d2p_frames_ready", "d2p_pull", "d2p_pull_f64", "d2p_stats",
+    "d2p_create", "d2p_destroy", "d2p_push", "d2p_flush", "d2p_set_push_threshold", "d2p_finish", "d2p_frames_ready", "d2p_pull", "d2p_pull_f64", "d2p_stats",
     "d2p_convert_host", "d2p_check_level", "d2p_host_alloc", "d2p_host_free",
     "d2p_batch_create", "d2p_batch_destroy", "d2p_batch_run", "d2p_batch_convert_host", "d2p_batch_launches",
     "d2p_batch_stats", "d2p_total_frames", "d2p_block_range", "d2p_batch_run_blocks",
@@ -114,6 +114,8 @@ def lib():
     L.d2p_destroy.restype = None
     L.d2p_push.argtypes = [vp, vp, C.c_size_t]
     L.d2p_finish.argtypes = [vp]
+    L.d2p_flush.argtypes = [vp]
+    L.d2p_set_push_threshold.argtypes = [vp, C.c_size_t]
     L.d2p_frames_ready.restype = C.c_uint64
     L.d2p_frames_ready.argtypes = [vp]
     L.d2p_pull.argtypes = [vp, vp, C.c_size_t, C.POINTER(C.c_uint64)]

@@ -562,6 +562,10 @@ struct d2p_ctx {
     Launcher launcher;
     cudaStream_t stream = nullptr;
     std::vector<uint8_t> pending;   // host bytes not yet forming a whole block group
+    // small pushes (the reference hands over one 4096-byte block per channel at a time) are gathered in pinned memory
+    // and shipped as one copy + one launch when `push_threshold` bytes have accumulated (or at d2p_flush / d2p_finish)
+    uint8_t* h_stage = nullptr;
+    size_t staged = 0, push_threshold = (size_t)8 << 20;
     uint8_t* d_in[2] = {nullptr, nullptr};
     size_t d_in_cap[2] = {0, 0};
     int cur = 0;
@@ -744,18 +748,17 @@ void d2p_destroy(d2p_ctx* ctx) {
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     for (OutChunk& oc : ctx->ready) { if (oc.d_pcm) cudaFree(oc.d_pcm); if (oc.d_f64) cudaFree(oc.d_f64); }
     for (int i = 0; i < 2; ++i) if (ctx->d_in[i]) cudaFree(ctx->d_in[i]);
+    if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     ctx->launcher.destroy();
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     free_device_plan(ctx->dp);
     delete ctx;
 }
 
-int d2p_push(d2p_ctx* ctx, const uint8_t* raw, size_t nbytes) {
-    if (!ctx || (!raw && nbytes)) return set_err(D2P_ERR_INVALID_ARG, "null argument");
-    if (ctx->finished) return set_err(D2P_ERR_STATE, "push after finish");
+// Copy `nbytes` to the device and launch every frame that became computable.
+static int ctx_ship(d2p_ctx* ctx, const uint8_t* raw, size_t nbytes) {
     if (nbytes == 0) return D2P_OK;
     const d2p_config& c = ctx->dp->plan.cfg;
-    CK(cudaSetDevice(c.device));
     const size_t G = group_bytes(c);
     // whole groups available = pending + raw
     const size_t total = ctx->pending.size() + nbytes;
@@ -774,12 +777,54 @@ int d2p_push(d2p_ctx* ctx, const uint8_t* raw, size_t nbytes) {
     return ctx_process(ctx, ctx->have_q, LLONG_MAX, 0, false);
 }
 
+static int ctx_flush(d2p_ctx* ctx) {
+    if (ctx->staged == 0) return D2P_OK;
+    const size_t n = ctx->staged;
+    ctx->staged = 0;
+    return ctx_ship(ctx, ctx->h_stage, n);
+}
+
+int d2p_push(d2p_ctx* ctx, const uint8_t* raw, size_t nbytes) {
+    if (!ctx || (!raw && nbytes)) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    if (ctx->finished) return set_err(D2P_ERR_STATE, "push after finish");
+    if (nbytes == 0) return D2P_OK;
+    CK(cudaSetDevice(ctx->dp->plan.cfg.device));
+    const size_t T = ctx->push_threshold;
+    if (T == 0 || nbytes >= T) {                       // large pushes go straight to the device
+        int st = ctx_flush(ctx);
+        return st != D2P_OK ? st : ctx_ship(ctx, raw, nbytes);
+    }
+    if (!ctx->h_stage) CK(cudaMallocHost((void**)&ctx->h_stage, 2 * T));
+    std::memcpy(ctx->h_stage + ctx->staged, raw, nbytes);          // staged < T and nbytes < T: fits in 2T
+    ctx->staged += nbytes;
+    return ctx->staged >= T ? ctx_flush(ctx) : D2P_OK;
+}
+
+int d2p_flush(d2p_ctx* ctx) {
+    if (!ctx) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    if (ctx->finished) return D2P_OK;
+    CK(cudaSetDevice(ctx->dp->plan.cfg.device));
+    return ctx_flush(ctx);
+}
+
+int d2p_set_push_threshold(d2p_ctx* ctx, size_t nbytes) {
+    if (!ctx) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    if (nbytes > ((size_t)1 << 30)) return set_err(D2P_ERR_INVALID_ARG, "push threshold above 1 GiB");
+    CK(cudaSetDevice(ctx->dp->plan.cfg.device));
+    int st = ctx_flush(ctx);
+    if (st != D2P_OK) return st;
+    if (ctx->h_stage) { cudaFreeHost(ctx->h_stage); ctx->h_stage = nullptr; }
+    ctx->push_threshold = nbytes;
+    return D2P_OK;
+}
+
 int d2p_finish(d2p_ctx* ctx) {
     if (!ctx) return set_err(D2P_ERR_INVALID_ARG, "null argument");
     if (ctx->finished) return D2P_OK;
-    ctx->finished = true;
     const d2p_config& c = ctx->dp->plan.cfg;
     CK(cudaSetDevice(c.device));
+    { int fs = ctx_flush(ctx); if (fs != D2P_OK) return fs; }
+    ctx->finished = true;
     const size_t per = ctx->pending.size() / c.channels;      // trailing partial group: split evenly (A1)
     if (per == 0) return ctx_process(ctx, ctx->have_q, LLONG_MAX, 0, true);   // frames held back for dither F
     const size_t take = per * c.channels;

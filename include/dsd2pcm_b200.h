@@ -115,8 +115,14 @@ const char* d2p_tap_table_name(int index);
 int  d2p_create(const d2p_config* cfg, d2p_ctx** out);
 void d2p_destroy(d2p_ctx* ctx);
 /* Feed container-order DSD payload bytes (any chunking; host memory).  Replaces the per-block
- * process_channel + write_to_buffer pair: all frames that become computable are produced on the GPU. */
+ * process_channel + write_to_buffer pair: all frames that become computable are produced on the GPU
+ * (see d2p_flush for when). */
 int  d2p_push(d2p_ctx* ctx, const uint8_t* raw, size_t nbytes);
+/* Pushes smaller than the push threshold (default 8 MiB; the reference hands over one 4096-byte block per channel at
+ * a time) are gathered in pinned memory and shipped as ONE copy + ONE launch when the threshold is reached, at
+ * d2p_flush() or at d2p_finish(): frames therefore become ready in bursts.  Threshold 0 ships every push at once. */
+int  d2p_flush(d2p_ctx* ctx);
+int  d2p_set_push_threshold(d2p_ctx* ctx, size_t nbytes);
 /* End of input: a trailing partial block group is split evenly between channels. */
 int  d2p_finish(d2p_ctx* ctx);
 /* Frames produced and not yet pulled. */

@@ -340,3 +340,31 @@ def test_level_check_device_resident_batch_and_silence():
     assert peak == 0.0 and np.isneginf(db)
     with pytest.raises(_capi.D2PError):
         d2p.Converter(cfg)                                         # the streaming context has no level-only mode
+
+
+@pytest.mark.parametrize("threshold", [0, 20000, None])
+def test_block_by_block_pushes_are_coalesced_and_exact(threshold):
+    """The reference's own call pattern: one 4096-byte block per channel per call (process_blocks).  Small pushes
+    are gathered in pinned memory and shipped per threshold / flush / finish; the frames are the same."""
+    raw = rand_payload(77, 2, 40)
+    ref = orclib.convert(raw, dsd_rate=1, out_rate=176400, bits=24, channels=2)
+    cfg = d2p.make_config(dsd_rate=1, out_rate=176400, bits=24, channels=2)
+    conv = d2p.Converter(cfg)
+    if threshold is not None:
+        conv.set_push_threshold(threshold)
+    pcm, ready_after_push = [], []
+    for off in range(0, raw.size, 4096):
+        conv.push(raw[off:off + 4096])
+        ready_after_push.append(conv.frames_ready())
+        if off == 20 * 8192:
+            conv.flush()
+            assert conv.frames_ready() > 0 or pcm                  # everything pushed so far is on its way
+        pcm.append(conv.pull())
+    conv.finish()
+    pcm.append(conv.pull())
+    conv.close()
+    assert np.array_equal(np.concatenate(pcm), ref.pcm)
+    if threshold == 0:
+        assert all(r > 0 for r in ready_after_push[3::2])          # every completed block group yields frames at once
+    if threshold is None:
+        assert sum(1 for r in ready_after_push if r > 0) <= 2      # 320 KiB < 8 MiB: only the explicit flush ships
