@@ -14,6 +14,7 @@
 #include <climits>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <map>
@@ -1095,7 +1096,12 @@ int d2p_batch_convert_host(d2p_batch* b, const uint8_t* raw, size_t nbytes, void
     if (c.out_format == D2P_OUT_PLANAR_32 || c.keep_f64)
         return set_err(D2P_ERR_INVALID_ARG, "host conversion produces interleaved packed PCM only");
     CK(cudaSetDevice(c.device));
-    return host_convert(*b->dp, b->launcher, b->pipe, raw, nbytes, pcm, out_cap_bytes, frames, (size_t)64 << 20);
+    static const size_t chunk = [] {                       // D2P_HOST_CHUNK_MB: pipeline granularity (tuning knob)
+        const char* e = std::getenv("D2P_HOST_CHUNK_MB");
+        const long mb = e ? std::atol(e) : 0;
+        return (size_t)(mb >= 1 && mb <= 1024 ? mb : 64) << 20;
+    }();
+    return host_convert(*b->dp, b->launcher, b->pipe, raw, nbytes, pcm, out_cap_bytes, frames, chunk);
 }
 
 int d2p_convert_host(const d2p_config* cfg, const uint8_t* raw, size_t nbytes, void* pcm, size_t out_cap_bytes,

@@ -48,7 +48,12 @@ def main():
     ap.add_argument("--minutes", type=float, default=60.0)
     ap.add_argument("--blocks", type=int, default=8)
     ap.add_argument("--only", default="3a,3b,4")
+    ap.add_argument("--shard", action="store_true",
+                    help="under torchrun: every rank converts only ITS time blocks of the payload (own GPU, own slice); "
+                         "rank 0 also converts the whole payload in one pass and compares the per-block digests")
     args = ap.parse_args()
+    if args.shard:
+        return shard_main(args)
 
     import torch
     import dsd2dxd_b200 as d2p
@@ -114,6 +119,76 @@ def main():
                           "plan": {k: info[k] for k in ("decim_ratio", "upsample_ratio", "num_stages", "tables")}}), flush=True)
         del d_in, d_out
         torch.cuda.empty_cache()
+
+
+def shard_main(args):
+    """SURVEY 8e on real GPUs: time blocks of ONE long payload spread over the ranks, no collective on the data path
+    (NCCL only gathers the 64-bit digests)."""
+    import torch
+    import torch.distributed as dist
+    import dsd2dxd_b200 as d2p
+    from dsd2dxd_b200 import shard
+
+    rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("WORLD_SIZE", 1), ("LOCAL_RANK", 0)))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    dist.init_process_group("nccl", device_id=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    for name in args.only.split(","):
+        kw = dict(CONFIGS[name])
+        what = kw.pop("what")
+        C = kw["channels"]
+        per_ch = int(args.minutes * 60 * 2822400 * kw["dsd_rate"] / 8) // 4096 * 4096
+        in_bytes = per_ch * C
+        cfg = d2p.make_config(block_size=4096, dither_seed=7, filt="E", device=local, **kw)
+        bps = d2p.plan(cfg)["bytes_per_sample"]
+        blocks = shard.split_payload(cfg, in_bytes, args.blocks, align_frames=16)
+        mine = shard.blocks_of_rank(blocks, rank, world)
+        gen = torch.Generator(device=dev)
+        gen.manual_seed(0x5D2DDD)
+        # the "file": every rank can read any part of it; a rank only ever touches the slices of its own blocks
+        d_in = torch.empty(in_bytes, dtype=torch.uint8, device=dev)
+        for off in range(0, in_bytes, 1 << 30):
+            n = min(1 << 30, in_bytes - off)
+            d_in[off:off + n] = torch.randint(0, 256, (n,), dtype=torch.uint8, device=dev, generator=gen)
+        batch = d2p.Batch(cfg)
+        outs = [torch.zeros(b.frame_count * C * bps + 16, dtype=torch.uint8, device=dev) for b in mine]
+        slices = [d_in[b.in_offset:b.in_offset + b.in_bytes].clone() for b in mine]      # the rank's private copies
+        dist.barrier()
+        torch.cuda.synchronize()
+        a, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        batch.run_blocks([dict(d_in=s_.data_ptr(), in_offset=b.in_offset, in_bytes=b.in_bytes, payload_bytes=in_bytes,
+                               first_frame=b.first_frame, frame_count=b.frame_count, d_out=o.data_ptr(),
+                               out_cap_bytes=o.numel(), dither_seed=7) for b, s_, o in zip(mine, slices, outs)], stream)
+        e.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([a.elapsed_time(e)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        digs = {b.index: digest(o[:b.frame_count * C * bps], torch) for b, o in zip(mine, outs)}
+        gathered = [None] * world
+        dist.all_gather_object(gathered, digs)
+        if rank == 0:
+            frames = d2p.frames_for_bytes(cfg, per_ch)
+            whole = torch.zeros(frames * C * bps + 16, dtype=torch.uint8, device=dev)
+            jobs = batch.make_jobs([dict(d_in=d_in.data_ptr(), in_bytes=in_bytes, d_out=whole.data_ptr(),
+                                         out_cap_bytes=whole.numel(), dither_seed=7)])
+            batch.run(jobs, stream)
+            torch.cuda.synchronize()
+            want = {b.index: digest(whole[b.first_frame * C * bps:(b.first_frame + b.frame_count) * C * bps], torch)
+                    for b in blocks}
+            got = {k: v for g in gathered for k, v in g.items()}
+            print(json.dumps({"config": name, "what": what, "minutes": args.minutes, "ranks": world, "blocks": len(blocks),
+                              "sharded_ms_max_over_ranks": float(t[0]), "dsd_samples_per_s": in_bytes * 8 / (float(t[0]) / 1e3),
+                              "blocks_equal_one_pass": got == want, "mismatching_blocks": [k for k in want if got.get(k) != want[k]]}),
+                  flush=True)
+            del whole
+        batch.close()
+        del d_in, outs, slices
+        torch.cuda.empty_cache()
+        dist.barrier()
+    dist.destroy_process_group()
 
 
 if __name__ == "__main__":
