@@ -825,10 +825,23 @@ __global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __gri
                         if (step_ph == 0 && relz <= rel0) {
                             // the usual case: a round advances a whole number of stage-2 periods (the lane's row of the
                             // phase-major tile never changes) and every output of the tile exists
-#pragma unroll 2
-                            for (int rel = rel0, d = d0; rel <= last_rel; rel += step_n, d += step_t, pd += step_q) {
+                            // two outputs per round trip: both windows are fetched and all ten look-ups issued before the
+                            // first store (stores to the stage-1 tile may alias the input tile as far as the compiler knows)
+                            int rel = rel0, d = d0;
+                            for (; rel + step_n <= last_rel; rel += 2 * step_n, d += 2 * step_t, pd += 2 * step_q) {
+                                const int w0 = d >> 5, d1 = d + step_t, w1 = d1 >> 5;
+                                const uint32_t z0 = __brev(__funnelshift_r(tw[w0], tw[w0 + 1], d & 31));   // bit j = x[t-j]
+                                const uint32_t z1 = __brev(__funnelshift_r(tw[w1], tw[w1 + 1], d1 & 31));
+                                double y0 = lds_f64<0>(__dp2a_lo(rlo, z0, tpl)), y1 = lds_f64<0>(__dp2a_lo(rlo, z1, tpl));
+                                if (GMAX > 1) { y0 = __dadd_rn(y0, lds_f64<8>(__dp2a_lo(rhi, z0, tpl))); y1 = __dadd_rn(y1, lds_f64<8>(__dp2a_lo(rhi, z1, tpl))); }
+                                if (GMAX > 2) { y0 = __dadd_rn(y0, lds_f64<16>(__dp2a_hi(rlo, z0, tpl))); y1 = __dadd_rn(y1, lds_f64<16>(__dp2a_hi(rlo, z1, tpl))); }
+                                if (GMAX > 3) { y0 = __dadd_rn(y0, lds_f64<24>(__dp2a_hi(rhi, z0, tpl))); y1 = __dadd_rn(y1, lds_f64<24>(__dp2a_hi(rhi, z1, tpl))); }
+                                if (GMAX > 4) { y0 = __dadd_rn(y0, lds_f64<32>(__dp2a_lo(rlo, z0, tpl))); y1 = __dadd_rn(y1, lds_f64<32>(__dp2a_lo(rlo, z1, tpl))); }
+                                pd[0] = y0; pd[step_q] = y1;
+                            }
+                            if (rel <= last_rel) {
                                 const int w = d >> 5;
-                                const uint32_t z = __brev(__funnelshift_r(tw[w], tw[w + 1], d & 31));   // bit j = x[t-j]
+                                const uint32_t z = __brev(__funnelshift_r(tw[w], tw[w + 1], d & 31));
                                 double y = lds_f64<0>(__dp2a_lo(rlo, z, tpl));
                                 if (GMAX > 1) y = __dadd_rn(y, lds_f64<8>(__dp2a_lo(rhi, z, tpl)));
                                 if (GMAX > 2) y = __dadd_rn(y, lds_f64<16>(__dp2a_hi(rlo, z, tpl)));
