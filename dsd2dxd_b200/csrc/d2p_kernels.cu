@@ -161,8 +161,35 @@ __device__ void stage_input(const KParams& P, const DevJob& J, unsigned char* ti
     if (P.layout == 'P') {
         const int nvec = nbytes >> 4;
         const bool fast = ((P.block_size & 15) == 0) && ((((uintptr_t)J.in) & 15) == 0) && ((J.base_q & 15) == 0);
-        for (int v = tid; v < nvec * C; v += nthr) {
-            const int c = v / nvec, idx = v - c * nvec;
+        // Interior chunks [i_lo, i_hi) of an LSB-first payload with power-of-two blocks (DSF): whole 16-byte pieces of
+        // the stream that need no transformation.  One 64-bit base per tile and channel, 32-bit arithmetic per chunk,
+        // asynchronous copies.  Only the few edge chunks (stream start / end, ragged tail) take the general loop.
+        int i_lo = 0, i_hi = 0;
+        if (fast && P.lsb_first && P.block_shift >= 4) {
+            const long long lo_q = J.base_q > 0 ? J.base_q : 0;
+            const long long hi_q = J.end_q < J.tail_q ? J.end_q : J.tail_q;
+            long long a = (lo_q - s_lo + 15) >> 4, b = (hi_q - s_lo) >> 4;
+            a = a < 0 ? 0 : (a > nvec ? nvec : a);
+            b = b < a ? a : (b > nvec ? nvec : b);
+            i_lo = (int)a; i_hi = (int)b;
+            if (i_hi > i_lo) {
+                const long long qr0 = s_lo + 16LL * i_lo - J.base_q;
+                const long long blk0 = qr0 >> P.block_shift;
+                const int w0 = (int)(qr0 & (P.block_size - 1)), mask = P.block_size - 1;
+                for (int c = 0; c < C; ++c) {
+                    const unsigned char* src0 = J.in + ((blk0 * C + c) << P.block_shift);
+                    unsigned char* dst = tiles + (size_t)c * P.tile_stride + 16 * i_lo;
+                    for (int i = tid; i < i_hi - i_lo; i += nthr) {
+                        const int r = w0 + 16 * i;
+                        cp_async16(dst + 16 * i, src0 + ((size_t)((r >> P.block_shift) * C) << P.block_shift) + (r & mask));
+                    }
+                }
+            }
+        }
+        const int nedge = nvec - (i_hi - i_lo);
+        for (int v = tid; v < nedge * C; v += nthr) {
+            const int c = v / nedge, e = v - c * nedge;
+            const int idx = e < i_lo ? e : e + (i_hi - i_lo);
             const long long q = s_lo + 16LL * idx;
             uint4 val = make_uint4(0, 0, 0, 0);
             if (fast && q >= J.base_q && q + 16 <= J.end_q && q + 16 <= J.tail_q) {
