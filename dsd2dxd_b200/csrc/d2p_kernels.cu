@@ -553,31 +553,40 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
     const bool staged_out = P.out_format == D2P_DEV_OUT_LE || P.out_format == D2P_DEV_OUT_BE;
     const size_t fb = (size_t)P.C * P.bps;
 
+    // tile headers (job look-up, 64-bit position arithmetic) are worked out by the producer warps only, one tile
+    // ahead, and handed to the consumers through shared memory
+    __shared__ TileInfo hdr[2];
     unsigned int tile = blockIdx.x;
+    TileInfo cur, prev;
+    cur.J = nullptr; prev.J = nullptr;
     if (tile < P.total_tiles && producer) {
-        const TileInfo t = lutfir_tile(P, tile);
-        stage_input(P, *t.J, inbuf, t.s_lo, t.nbytes, ptid, np);
+        cur = lutfir_tile(P, tile);
+        if (ptid == 0) hdr[0] = cur;
+        stage_input(P, *cur.J, inbuf, cur.s_lo, cur.nbytes, ptid, np);
         cp_async_wait_all();
     }
     __syncthreads();
 
     int j = 0;
     bool have_prev = false;
-    TileInfo prev;
     for (; tile < P.total_tiles; tile += gridDim.x, ++j) {
         const int bsel = j & 1;
-        const TileInfo t = lutfir_tile(P, tile);
         if (producer) {
             const unsigned int nxt = tile + gridDim.x;
+            TileInfo tn;
+            tn.J = nullptr;
             if (nxt < P.total_tiles) {
-                const TileInfo tn = lutfir_tile(P, nxt);
+                tn = lutfir_tile(P, nxt);
+                if (ptid == 0) hdr[bsel ^ 1] = tn;
                 stage_input(P, *tn.J, inbuf + (size_t)(bsel ^ 1) * P.in_buf_bytes, tn.s_lo, tn.nbytes, ptid, np);
             }
             if (have_prev && staged_out)
                 copy_out(prev.J->out + (size_t)(prev.f0 - prev.J->f_begin) * fb, obuf + (size_t)(bsel ^ 1) * P.ostage_bytes,
                          (int)(prev.nf * fb), ptid, np);
             cp_async_wait_all();
+            prev = cur; cur = tn;
         } else {
+            const TileInfo t = hdr[bsel];
             const unsigned char* tiles = inbuf + (size_t)bsel * P.in_buf_bytes;
             unsigned char* ostage = obuf + (size_t)bsel * P.ostage_bytes;
             const int items = P.C << P.tf_shift;                  // item = channel * TF + frame-in-tile
@@ -650,7 +659,7 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
                 base += pair ? 2 * ps : ps;
             }
         }
-        prev = t; have_prev = true;
+        have_prev = true;
         __syncthreads();
     }
     if (producer && have_prev && staged_out)
