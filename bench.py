@@ -135,6 +135,32 @@ def workload_config(args):
             "l2": "inputs+outputs per step are far larger than L2 (no flush needed)"}
 
 
+_FULL_AFFINITY = None
+
+
+def bind_to_gpu_numa(local):
+    """One process per GPU: run this rank's host thread (and, by first touch, its pinned staging memory) on the CPUs
+    NVML reports as local to the GPU.  Returns a short description for the JSON line; never fatal."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = int(vis.split(",")[local]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else local
+        h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = {64 * w + b for w, m in enumerate(words) for b in range(64) if (m >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            global _FULL_AFFINITY
+            _FULL_AFFINITY = os.sched_getaffinity(0)
+            os.sched_setaffinity(0, cpus)
+            return f"{len(cpus)} cpus local to gpu {idx}"
+    except Exception as e:      # noqa: BLE001
+        return f"unbound ({type(e).__name__})"
+    return "unbound"
+
+
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -153,6 +179,7 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the library has no CPU path")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = bind_to_gpu_numa(local)          # pinned host buffers of the e2e path then live next to this rank's GPU
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         # stdout carries exactly one JSON line: NCCL's own banner ("NCCL version ...") is sent to stderr instead
@@ -280,7 +307,7 @@ def main():
             "realtime_factor": value / (2 * 11289600.0),
             "e2e": {"value": e2e_value, "unit": "DSD samples/s", "h2d_bytes_per_step": nf * in_bytes,
                     "d2h_bytes_per_step": nf * out_bytes, "files_per_step": nf, "timer": "wall clock around the synchronous host call",
-                    "realtime_factor": e2e_value / (2 * 11289600.0), "matches_device_path": same,
+                    "realtime_factor": e2e_value / (2 * 11289600.0), "matches_device_path": same, "host_affinity": numa,
                     "copies_alone": {"what": "bare pinned H2D of one file's payload + D2H of its PCM on two streams, rank 0",
                                      "seconds_per_file": copy_file_s, "h2d_gbs": in_bytes / copy_file_s / 1e9,
                                      "d2h_gbs": out_bytes / copy_file_s / 1e9,
@@ -298,6 +325,8 @@ def main():
             "clocks": clocks,
         }
         if not args.no_cpu:
+            if _FULL_AFFINITY:                       # the CPU arm uses every host core, not just the GPU's neighbours
+                os.sched_setaffinity(0, _FULL_AFFINITY)
             line["cpu_baseline"] = cpu_baseline(args, os.cpu_count() or 1)
         print(json.dumps(line))
     if world > 1:
