@@ -272,6 +272,15 @@ def write_pcm_file(path, container, bits, channels, rate, payload, frames):
                                                payload.ctypes.data, frames))
 
 
+def write_flac_file(path, bits, channels, rate, payload, frames, comments=()):
+    """FLAC file from packed little-endian interleaved PCM as the kernels emit it (d2p_write_flac_file;
+    the reference's save_flac_file, rd/audio_file.rs:454-573).  `comments`: "KEY=value" strings."""
+    payload = np.ascontiguousarray(payload, dtype=np.uint8)
+    arr = (C.c_char_p * max(len(comments), 1))(*[c.encode() for c in comments])
+    _capi.check(_capi.lib().d2p_write_flac_file(str(path).encode(), bits, channels, rate, payload.ctypes.data, frames,
+                                                arr if comments else None, len(comments)))
+
+
 def convert_file(in_path, out_path, out_rate=352800, filt="E", bits=24, dither="X", level_db=0.0, container="W",
                  dither_seed=0, device=0, dsf_stop_at_sample_count=False, raw_channels=2, raw_layout="P",
                  raw_lsb_first=True, raw_dsd_rate=1, raw_block_size=4096):

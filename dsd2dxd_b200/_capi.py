@@ -83,7 +83,7 @@ EXPORTS = [
     "d2p_convert_host", "d2p_check_level", "d2p_host_alloc", "d2p_host_free",
     "d2p_batch_create", "d2p_batch_destroy", "d2p_batch_run", "d2p_batch_convert_host", "d2p_batch_launches",
     "d2p_batch_stats", "d2p_total_frames", "d2p_block_range", "d2p_batch_run_blocks",
-    "d2p_container_parse", "d2p_container_open", "d2p_pcm_header", "d2p_write_pcm_file", "d2p_convert_file",
+    "d2p_container_parse", "d2p_container_open", "d2p_pcm_header", "d2p_write_pcm_file", "d2p_write_flac_file", "d2p_convert_file",
 ]
 
 _lib = None
@@ -146,6 +146,7 @@ def lib():
     L.d2p_pcm_header.restype = C.c_size_t
     L.d2p_pcm_header.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint64, vp, C.c_size_t]
     L.d2p_write_pcm_file.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_uint32, vp, C.c_uint64]
+    L.d2p_write_flac_file.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_uint32, vp, C.c_uint64, C.POINTER(C.c_char_p), C.c_int]
     L.d2p_convert_file.argtypes = [C.POINTER(FileOptions), C.c_char_p, C.c_char_p, C.POINTER(FileResult)]
     _lib = L
     return L

@@ -268,6 +268,7 @@ size_t d2p_pcm_header(int container, int bits, int channels, uint32_t rate, uint
 int d2p_write_pcm_file(const char* path, int container, int bits, int channels, uint32_t rate,
                        const void* payload, uint64_t frames) {
     if (!path || (!payload && frames)) return api_set_error(D2P_ERR_INVALID_ARG, "null argument");
+    if (container == D2P_FILE_FLAC) return d2p_write_flac_file(path, bits, channels, rate, payload, frames, nullptr, 0);
     Bytes h;
     if (!build_header(container, bits, channels, rate, frames, &h)) {
         if (container == D2P_FILE_AIFF && bits == 32)
@@ -290,8 +291,8 @@ int d2p_convert_file(const d2p_file_options* opt, const char* in_path, const cha
     if (opt->out_container == D2P_FILE_AIFF && opt->bits == 32)
         return api_set_error(D2P_ERR_BIT_DEPTH, "32 bit float only allowed with wav, aifc, or stdout");
     if (opt->out_container != D2P_FILE_WAV && opt->out_container != D2P_FILE_AIFF && opt->out_container != D2P_FILE_AIFC &&
-        opt->out_container != D2P_FILE_RAW)
-        return api_set_error(D2P_ERR_INVALID_ARG, "output container must be W, A, C or S");
+        opt->out_container != D2P_FILE_RAW && opt->out_container != D2P_FILE_FLAC)
+        return api_set_error(D2P_ERR_INVALID_ARG, "output container must be W, A, C, S or F");
 
     d2p_container_info& ci = R.in;
     FileCloser fc{std::fopen(in_path, "rb")};
@@ -356,6 +357,11 @@ int d2p_convert_file(const d2p_file_options* opt, const char* in_path, const cha
     R.frames = frames;
     st = d2p_write_pcm_file(out_path, opt->out_container, opt->bits, ci.channels, opt->out_rate, h_out, frames);
     if (st != D2P_OK) return st;
+    if (opt->out_container == D2P_FILE_FLAC) {                     // compressed: the size is whatever the encoder produced
+        FileCloser of{std::fopen(out_path, "rb")};
+        if (of.f && std::fseek(of.f, 0, SEEK_END) == 0) R.out_bytes = (uint64_t)std::ftell(of.f);
+        return D2P_OK;
+    }
     Bytes h;
     build_header(opt->out_container, opt->bits, ci.channels, opt->out_rate, frames, &h);
     R.out_bytes = h.v.size() + frames * (uint64_t)ci.channels * (uint64_t)pi.bytes_per_sample;

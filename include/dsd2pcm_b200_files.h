@@ -14,7 +14,10 @@
  *            rd/lib.rs:171-182, 275-281, rd/pcm_writer.rs:300-318
  * (rd/ = src/rdsd2pcm/src/ of the reference.)  Host-side byte formatting only: every sample still
  * comes from the CUDA kernels; the payload reaches the file in the byte order the kernel packed it.
- * FLAC encoding, ID3 -> tag copy and output naming stay out of scope.
+ *   flac     AudioFile::save_flac_file   rd/audio_file.rs:454-573   (which integers go in: 16 / 20 / 24 bit, float
+ *            written as 24 bit; the bitstream is the encoder's own -- the reference delegates it to the
+ *            flac-codec crate -- and is checked by decode equality)
+ * ID3 -> tag mapping and output naming stay out of scope.
  */
 #ifndef DSD2PCM_B200_FILES_H
 #define DSD2PCM_B200_FILES_H
@@ -27,7 +30,8 @@ extern "C" {
 
 enum { D2P_CONTAINER_DSF = 'S', D2P_CONTAINER_DFF = 'F', D2P_CONTAINER_RAW = 'R' };
 /* Output containers: the reference CLI's -o letters that carry PCM (src/main.rs:196-204) */
-enum { D2P_FILE_WAV = 'W', D2P_FILE_AIFF = 'A', D2P_FILE_AIFC = 'C', D2P_FILE_RAW = 'S' /* stdout-style headerless LE */ };
+enum { D2P_FILE_WAV = 'W', D2P_FILE_AIFF = 'A', D2P_FILE_AIFC = 'C', D2P_FILE_RAW = 'S' /* stdout-style headerless LE */,
+       D2P_FILE_FLAC = 'F' };
 
 typedef struct d2p_container_info {
     int32_t  format;          /* D2P_CONTAINER_* */
@@ -58,9 +62,16 @@ int d2p_container_open(const char* path, d2p_container_info* info);
  * AIFF with 32-bit float, bits outside 16/20/24/32).  AIFC places a FLLR chunk so that the sample
  * data starts on a 4096-byte boundary (rd/audio_file.rs:331-343); the header can therefore be 4 KiB. */
 size_t d2p_pcm_header(int container, int bits, int channels, uint32_t rate, uint64_t frames, uint8_t* out, size_t cap);
-/* header + payload -> file */
+/* header + payload -> file (D2P_FILE_FLAC: d2p_write_flac_file without comments) */
 int d2p_write_pcm_file(const char* path, int container, int bits, int channels, uint32_t rate,
                        const void* payload, uint64_t frames);
+/* FLAC file from `frames` frames of packed LITTLE-endian interleaved samples as the kernels emit them
+ * (16: int16; 20: left-aligned in 3 bytes; 24: 3 bytes; 32: float32).  Like the reference: 20-bit samples are
+ * stored unshifted at bits_per_sample 20, float becomes (clamp(x,-1,1) * 8388607.0f) truncated at 24 bits, zero
+ * channels or zero frames is an error.  `comments` are n_comments "KEY=value" strings for the VORBIS_COMMENT
+ * block (may be NULL / 0).  Lossless: decoding returns exactly those integers; STREAMINFO carries their MD5. */
+int d2p_write_flac_file(const char* path, int bits, int channels, uint32_t rate, const void* payload, uint64_t frames,
+                        const char* const* comments, int n_comments);
 
 typedef struct d2p_file_options {
     uint32_t out_rate;        /* -r */
