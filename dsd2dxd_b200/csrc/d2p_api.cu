@@ -234,6 +234,9 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
         k.lm_cons = cons;
         k.sigma2 = (p.D2 - p.h2 % p.D2) % p.D2;
         k.sigma3 = p.nstages == 3 ? (p.D3 - p.h3 % p.D3) % p.D3 : 0;
+        k.fir2_rf = (2 * p.h2 - 1 + k.sigma2) % p.D2; k.fir2_q = (2 * p.h2 - 1 + k.sigma2) / p.D2;
+        k.fir3_rf = p.nstages == 3 ? (2 * p.h3 - 1 + k.sigma3) % p.D3 : 0;
+        k.fir3_q = p.nstages == 3 ? (2 * p.h3 - 1 + k.sigma3) / p.D3 : 0;
         k.inv_d2 = (65536 + p.D2 - 1) / p.D2;
         k.inv_d3 = p.nstages == 3 ? (65536 + p.D3 - 1) / p.D3 : 0;
         // row per byte value; block (u + A*cyc) holds the tables of phase (m1 * (A*cyc + u)) mod L

@@ -83,6 +83,7 @@ struct KParams {
     long long e0;
     int h2, D2, h3, D3;
     int sigma2, sigma3;       // element shift of the phase-major tiles: -h (mod D), aligns the FIR walkers' wraps
+    int fir2_rf, fir2_q, fir3_rf, fir3_q;   // (2h-1+sigma) mod D and div D: row / column of tap 0's front element
     int inv_d2, inv_d3;       // ceil(65536 / D): (x * inv) >> 16 == x / D for the small x the kernels divide
     int s1_cap, s2_cap;       // doubles per channel slot of the stage-1 / stage-2 tiles
     int NB;                   // channel slots kept in flight together

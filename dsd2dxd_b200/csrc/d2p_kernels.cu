@@ -709,10 +709,10 @@ __device__ __forceinline__ double fir_run(const double* __restrict__ taps, const
 }
 
 __device__ __forceinline__ double fir_sym_t(const double* __restrict__ taps, const double* __restrict__ col, int h, int D,
-                                            int pitch, int sigma) {
-    const int ef = 2 * h - 1 + sigma;                               // front element of tap 0 (T0 = 2h-1), shifted
-    int rf = ef % D;
-    const double* pf = col + rf * pitch + ef / D;
+                                            int pitch, int sigma, int rf0, int q0) {
+    // front element of tap 0 (T0 = 2h-1), shifted: ef = 2h-1+sigma, rf0 = ef mod D, q0 = ef div D (host-computed)
+    int rf = rf0;
+    const double* pf = col + rf * pitch + q0;
     const double* pb = col + sigma * pitch;                         // back element of tap 0: row sigma == D-1-rf, column 0
     const int wrap = D * pitch - 1;
     double total = 0.0;
@@ -912,7 +912,7 @@ __global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __gri
                     while (idx >= cnt2) { idx -= cnt2; ++sl; }
                     double tot = 0.0;
                     if (H.k2_lo + idx >= 0)
-                        tot = fir_sym_t(P.c2, s1 + (size_t)sl * P.s1_cap + (idx + H.j2_0), P.h2, P.D2, P.pitch2, P.sigma2);
+                        tot = fir_sym_t(P.c2, s1 + (size_t)sl * P.s1_cap + (idx + H.j2_0), P.h2, P.D2, P.pitch2, P.sigma2, P.fir2_rf, P.fir2_q);
                     if (P.nstages == 2) em.emit(P, J, ostage, cb + sl, f0 + idx, idx, tot);
                     else {
                         const int e3 = idx + P.sigma3;
@@ -926,7 +926,7 @@ __global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __gri
                     for (int item = tid; item < nbc * nf; item += NCONS) {
                         int sl = 0, idx = item;
                         while (idx >= nf) { idx -= nf; ++sl; }
-                        const double y = fir_sym_t(P.c3, s2 + (size_t)sl * P.s2_cap + idx, P.h3, P.D3, P.pitch3, P.sigma3);
+                        const double y = fir_sym_t(P.c3, s2 + (size_t)sl * P.s2_cap + idx, P.h3, P.D3, P.pitch3, P.sigma3, P.fir3_rf, P.fir3_q);
                         em.emit(P, J, ostage, cb + sl, f0 + idx, idx, y);
                     }
                 }
