@@ -734,6 +734,7 @@ struct LmTile {                 // per-tile header, computed by one thread
     const DevJob* J;
     long long f0, k2_lo, s_lo;
     int nf, cnt2, j2_0, last_rel, relz, back, dA, nbytes;
+    int nch;                    // = P.C; read back from the header so that the channel-group loop keeps its own counter
 };
 
 __device__ __forceinline__ void lm_tile_header(const KParams& P, unsigned int tile, LmTile& H) {
@@ -742,7 +743,7 @@ __device__ __forceinline__ void lm_tile_header(const KParams& P, unsigned int ti
     const long long f0 = J.f_begin + (long long)(tile - J.tile_begin) * P.TF;
     const long long left = J.f_begin + J.f_count - f0;
     const int nf = left < P.TF ? (int)left : P.TF;
-    H.f0 = f0; H.nf = nf;
+    H.f0 = f0; H.nf = nf; H.nch = P.C;
     // stage-2 output range feeding the tile (for 2 stages it *is* the tile)
     long long k2_lo, k2_hi;
     if (P.nstages == 3) { k2_lo = (P.h3 - 1) + f0 * P.D3 - (2 * P.h3 - 1); k2_hi = (P.h3 - 1) + (f0 + nf - 1) * P.D3; }
@@ -851,8 +852,12 @@ __global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __gri
             const int e0 = rel0 + P.sigma2;                         // shifted element index (see fir_sym_t)
             const int q0 = (e0 * P.inv_d2) >> 16, p0 = e0 - q0 * P.D2;
 
-            for (int cb = 0; cb < P.C; cb += P.NB) {
-                const int nbc = P.C - cb < P.NB ? P.C - cb : P.NB;
+            // the 448-consumer build reads the channel count back from the tile header: an opaque bound keeps the
+            // compiler from collapsing the tile and channel-group loops into one counter with divisions per iteration
+            // (the 64-register 896-consumer build is better off without the extra live value)
+            const int nch = NCONS == kLmConsumersSmall ? H.nch : P.C;
+            for (int cb = 0; cb < nch; cb += P.NB) {
+                const int nbc = nch - cb < P.NB ? nch - cb : P.NB;
                 // ---- stage 1 (A1 + A7/A8) ----
                 if (u < A) {
                     for (int sl = 0; sl < nbc; ++sl) {
@@ -930,7 +935,7 @@ __global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __gri
                         em.emit(P, J, ostage, cb + sl, f0 + idx, idx, y);
                     }
                 }
-                if (cb + P.NB < P.C) consumer_sync<NCONS>();               // s1/s2 are reused by the next channel group
+                if (cb + P.NB < nch) consumer_sync<NCONS>();               // s1/s2 are reused by the next channel group
             }
         }
         __syncthreads();
