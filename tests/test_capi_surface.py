@@ -72,3 +72,79 @@ def test_compute_entries_fail_loudly_without_a_gpu():
     assert e.value.status == 5 and "no CPU path" in str(e.value)
     with pytest.raises(d2p.D2PError):
         d2p.convert_host(d2p.make_config(), np.zeros(8192, dtype=np.uint8))
+
+
+# ---- the reference-side binding (integration/dsd2pcm-b200-sys) stays in step with the headers ----------------
+def _headers():
+    text = "".join(open(os.path.join(ROOT, "include", h)).read() for h in ("dsd2pcm_b200.h", "dsd2pcm_b200_files.h"))
+    return re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+
+
+def _rust():
+    return open(os.path.join(ROOT, "integration", "dsd2pcm-b200-sys", "src", "lib.rs")).read()
+
+
+def test_rust_ffi_crate_declares_exactly_the_header_functions():
+    rs = _rust()
+    assert sorted(set(re.findall(r"pub fn (d2p_[a-z0-9_]+)\s*\(", rs))) == declared_symbols()
+
+
+C_TO_RUST = {"int32_t": "i32", "uint32_t": "u32", "int64_t": "i64", "uint64_t": "u64", "double": "f64", "float": "f32",
+             "const void*": "*const c_void", "void*": "*mut c_void", "double*": "*mut f64", "d2p_container_info": "d2p_container_info"}
+
+
+def _c_struct_fields(name):
+    body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (name, name), _headers(), flags=re.S).group(1)
+    fields = []
+    for decl in body.split(";"):
+        decl = " ".join(decl.split())
+        if not decl:
+            continue
+        m = re.match(r"(const void\*|void\*|double\*|[a-z0-9_]+)\s+(.*)", decl)
+        ctype, names = m.group(1), m.group(2)
+        for nm in names.split(","):
+            nm = nm.strip()
+            arr = re.findall(r"\[(\d+)\]", nm)
+            fields.append((re.sub(r"\[.*", "", nm), ctype, [int(a) for a in arr]))
+    return fields
+
+
+def _rust_struct_fields(name):
+    body = re.search(r"pub struct %s \{(.*?)\n\}" % name, _rust(), flags=re.S).group(1)
+    return [(m.group(1), m.group(2).strip()) for m in re.finditer(r"pub (\w+): ([^,\n]+),", body)]
+
+
+@pytest.mark.parametrize("name", ["d2p_config", "d2p_plan_info", "d2p_job", "d2p_block_job", "d2p_container_info",
+                                  "d2p_file_options", "d2p_file_result"])
+def test_rust_structs_mirror_the_c_layout(name):
+    cf, rf = _c_struct_fields(name), _rust_struct_fields(name)
+    assert len(cf) == len(rf), (cf, rf)
+    for (cn, ct, arr), (rn, rt) in zip(cf, rf):
+        assert rn == cn or (cn, rn) == ("in", "input")          # `in` is a Rust keyword
+        if ct == "char":
+            want = "c_char"
+        else:
+            want = C_TO_RUST[ct]
+        for a in reversed(arr):
+            want = f"[{want}; {a}]"
+        assert rt == want, (name, cn, rt, want)
+
+
+def test_rust_constants_match_the_header_enums():
+    hs, rs = _headers(), _rust()
+    c_vals = {}
+    for m in re.finditer(r"\b(D2P_[A-Z0-9_]+)\s*=\s*('.'|\d+)", hs):
+        v = m.group(2)
+        c_vals[m.group(1)] = ord(v[1]) if v.startswith("'") else int(v)
+    r_vals = {}
+    for m in re.finditer(r"pub const (D2P_[A-Z0-9_]+): \w+ = (b'.' as i32|\d+);", rs):
+        v = m.group(2)
+        r_vals[m.group(1)] = ord(v[2]) if v.startswith("b'") else int(v)
+    r_vals.pop("D2P_ABI_VERSION")
+    assert r_vals == c_vals
+
+
+def test_ctypes_structs_have_the_c_field_order():
+    for cname, cls in (("d2p_config", _capi.Config), ("d2p_container_info", _capi.ContainerInfo),
+                       ("d2p_file_options", _capi.FileOptions)):
+        assert [f[0] for f in cls._fields_] == [c[0] for c in _c_struct_fields(cname)], cname
