@@ -324,7 +324,7 @@ def main():
                     "frac_at_observed_clock": lookups / (kernel_ms / 1e3) / (SM_COUNT * LDS_LOOKUPS_PER_CLK_SM * sm_mhz * 1e6)},
             "clocks": clocks,
         }
-        if not args.no_cpu:
+        if not args.no_cpu and world == 1:           # the CPU leg is reported at N=1 only
             if _FULL_AFFINITY:                       # the CPU arm uses every host core, not just the GPU's neighbours
                 os.sched_setaffinity(0, _FULL_AFFINITY)
             line["cpu_baseline"] = cpu_baseline(args, os.cpu_count() or 1)
