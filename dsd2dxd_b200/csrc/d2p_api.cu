@@ -256,16 +256,20 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
         // integer path: pick the replication (skew depth K) and the tile size together.  More replicas mean
         // fewer idle skew steps per frame (nt / (nt + K - 1)) but a larger LUT; one persistent CTA per SM.
         double best_score = 0.0; LutLayout bestL; int best_tf = 0;
+        int setF = 1, setDW = 1;
+        lutfir_set_shape(p.bpo, &setF, &setDW);                   // a lane runs setF neighbouring frames in lockstep
         for (int K = 1; K <= 16; K <<= 1) {
             if (K > 1 && K - 1 > p.nt) continue;
             const LutLayout L = make_lut_layout(p.nt, K);
-            for (int tf = 2048; tf >= 64; tf >>= 1) {
+            for (int sl = 1024; sl >= 32; sl >>= 1) {              // slots (frame sets) per channel tile
+                const int tf = setF * sl;
                 int ts, ib, os; size_t sm;
                 lutfir_geometry(p, L, tf, &ts, &ib, &os, &sm);
                 if (sm > budget) continue;
                 const double steps = 4.0 * ((p.nt + K - 1 + 3) / 4);
-                const double ipt = (double)tf * cfg.channels / kMaxThreads;     // frames per consumer thread per tile
-                const double score = (p.nt / steps) * (ipt / (ipt + 0.35));
+                const double spt = (double)sl * cfg.channels / kMaxThreads;     // frame sets per consumer thread per tile
+                const double busy = spt / std::ceil(spt);                       // idle threads of the last round
+                const double score = (p.nt / steps) * busy * (spt / (spt + 0.12));
                 if (score > best_score) { best_score = score; bestL = L; best_tf = tf; }
                 break;
             }
@@ -273,7 +277,9 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
         if (!best_tf) return set_err(D2P_ERR_NOMEM, "filter LUT and tiles do not fit in shared memory");
         const LutLayout& L = bestL;
         k.TF = best_tf;
-        k.tf_shift = 0; while ((1 << k.tf_shift) < best_tf) ++k.tf_shift;
+        k.setF = setF; k.setDW = setDW;
+        k.sl_shift = 0; while ((setF << k.sl_shift) < best_tf) ++k.sl_shift;
+        k.fpw_shift = p.bpo >= 4 ? 0 : (p.bpo == 2 ? 1 : 2);
         lutfir_geometry(p, L, best_tf, &k.tile_stride, &k.in_buf_bytes, &k.ostage_bytes, &dp->smem);
         k.lutK = L.K; k.lut_row_bytes = L.slots * 8;
         for (int r = 0; r < 16; ++r) k.lut_st[r] = r < L.R ? L.st[r] : 0;

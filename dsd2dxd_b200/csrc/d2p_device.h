@@ -75,7 +75,9 @@ struct KParams {
     int ngroups, gp_lo, gp_hi;   // 4-step groups per frame; [gp_lo, gp_hi) need no activity guard
     int last_steps;              // steps of the last group that any lane still needs (1..4)
     int zpad_bytes;              // zero region in front of the LUT (idle skew steps read 0.0 from it)
-    int tf_shift;                // TF == 1 << tf_shift on the integer path
+    // frame sets of the integer path: a lane runs setF neighbouring frames (setDW tile words apart) in lockstep;
+    // TF == setF << sl_shift (slots per channel tile), fpw_shift = log2(frames per 32-bit stream word)
+    int setF, setDW, sl_shift, fpw_shift;
     int nc;                      // consumer threads (the remaining threads of the CTA stage tiles)
     int in_buf_bytes, ostage_bytes;   // per buffer (both are double-buffered)
     // L/M path (A6-A10)

@@ -401,7 +401,7 @@ __device__ __forceinline__ TileInfo lutfir_tile(const KParams& P, unsigned int t
     TileInfo t;
     const DevJob& J = find_job(P, tile);
     t.J = &J;
-    t.f0 = J.f_begin + ((long long)(tile - J.tile_begin) << P.tf_shift);
+    t.f0 = J.f_begin + (long long)(tile - J.tile_begin) * P.TF;
     const long long left = J.f_begin + J.f_count - t.f0;
     t.nf = left < P.TF ? (int)left : P.TF;
     const long long k0 = t.f0 + (P.h - 1);                        // delay_count = h-1 frames are discarded (A4)
@@ -430,53 +430,62 @@ __device__ __forceinline__ double lds_f64(uint32_t saddr) {
 //               it starts at +0.0 and x + y is -0.0 only if both are).
 struct LaneLut { uint32_t rlo, rhi; int dz, c; };
 
-// Two frames (A, B) of one lane in lockstep.  Both frames sit at the same table index at every step, so
-// the skew guard, the slot address and the loop bookkeeping are paid once per pair, and the two dependent
-// DADD chains interleave (ILP 2).  B's bytes are A's bytes dW words further on (same byte alignment).
-// K: where frame A starts; tp0: shared-memory address of the lane's slot at step 0.
-// PAIR = false: frame A alone (tiles too small to give every consumer thread two frames).
+// F frames of one lane in lockstep ("frame set").  The frames are neighbours in time: frame f+1 ends 4*DW bytes
+// after frame f (DW words; bpo < 4 packs 4/bpo frames into a word, those go to neighbouring lanes).  All frames
+// of the set sit at the same table index at every step, so the skew guard, the slot address and the loop
+// bookkeeping are paid once per set and the F dependent DADD chains interleave.  Because the frames are one (DW)
+// word apart, their 4-byte groups are one sliding window over the byte stream: group g of frame f is the word
+// that frame f-1 used at group g-DW (forward half), f+1 at g-DW (mirrored half).  Per group and half a lane
+// therefore loads ONE tile word, funnel-shifts once (and bit-reverses once for the mirrored half), whatever F is.
 //
-// Where a lane's frame starts in its channel tile: word pointers and funnel shifts of the two byte streams.
+// Where a lane's set starts in its channel tile: word pointers and funnel shifts of the two byte streams.
 //   forward half : step u reads byte jr + c - u  (group g: bytes a-4g .. a-4g+3 with a = jr + c - 3)
 //   mirrored half: step u reads byte jr - (2nt-1) - c + u
-// jr: tile-relative index of the frame's newest byte; c: the lane's skew.
-struct FrameCursor { const uint32_t* pf; const uint32_t* pb; int fsh, bsh; };
-__device__ __forceinline__ FrameCursor frame_cursor(const uint32_t* tw, int jr, int c, int nt) {
-    FrameCursor k;
-    const int a = jr + c - 3, b = jr - (2 * nt - 1) - c;
-    k.pf = tw + (a >> 2); k.fsh = (a & 3) * 8;
-    k.pb = tw + (b >> 2); k.bsh = (b & 3) * 8;
-    return k;
-}
-
-template <bool PAIR>
-__device__ __forceinline__ void lutfir_pair(const KParams& P, const LaneLut& L, const FrameCursor& K, int dW,
-                                            uint32_t tp0, double& yA, double& yB) {
+// jr: tile-relative index of the newest byte of the set's first frame; c: the lane's skew.
+template <int F, int DW>
+__device__ __forceinline__ void lutfir_set(const KParams& P, const LaneLut& L, const uint32_t* tw, int jr,
+                                           uint32_t tp0, double (&y)[F]) {
+    constexpr int WS = (F - 1) * DW + 1;          // window: frame f reads entry f*DW
     const int nt = P.nt;
-    const uint32_t* pf = K.pf;
-    const uint32_t* pb = K.pb;
-    const int fsh = K.fsh, bsh = K.bsh;
     const int c = L.c;
-    uint32_t fhA = pf[1], fhB = PAIR ? pf[1 + dW] : 0u;
-    uint32_t blA = pb[0], blB = PAIR ? pb[dW] : 0u;
-    // the words of the NEXT group are fetched one group ahead, so that a group never waits on its own tile loads
-    uint32_t nfA = pf[0], nfB = PAIR ? pf[dW] : 0u, nbA = pb[1], nbB = PAIR ? pb[1 + dW] : 0u;
-    double accA = 0.0, accB = 0.0;
+    const int a = jr + c - 3, b = jr - (2 * nt - 1) - c;
+    const uint32_t* pf = tw + (a >> 2);
+    const uint32_t* pb = tw + (b >> 2);
+    const int fsh = (a & 3) * 8, bsh = (b & 3) * 8;
+    uint32_t qf[WS], qb[WS];                      // qf[j]: forward group of window slot j;  qb[j]: mirrored, bit-reversed
+    uint32_t wf_lo, wf_nx, wb_hi, wb_nx;          // raw tile words at the window edges and the prefetched next ones
+    {
+        uint32_t w[WS + 1];
+#pragma unroll
+        for (int j = 0; j <= WS; ++j) w[j] = pf[j];
+#pragma unroll
+        for (int j = 0; j < WS; ++j) qf[j] = __funnelshift_r(w[j], w[j + 1], fsh);
+        wf_lo = w[0]; wf_nx = pf[-1];
+#pragma unroll
+        for (int j = 0; j <= WS; ++j) w[j] = pb[j];
+#pragma unroll
+        for (int j = 0; j < WS; ++j) qb[j] = __brev(__funnelshift_r(w[j], w[j + 1], bsh));
+        wb_hi = w[WS]; wb_nx = pb[WS + 1];
+    }
+    double acc[F];
+#pragma unroll
+    for (int f = 0; f < F; ++f) acc[f] = 0.0;
     uint32_t tp = tp0;
     int i0 = -c;
     const int gp_lo = P.gp_lo, gp_hi = P.gp_hi, ng = P.ngroups;
     int g = 0;
-#define D2P_FETCH()                                                                \
-        const uint32_t flA = nfA, flB = nfB, bhA = nbA, bhB = nbB;                 \
+    // the words of the NEXT group are fetched one group ahead, so that a group never waits on its own tile loads
+#define D2P_ADVANCE()                                                              \
+    {                                                                              \
+        const uint32_t nqf = __funnelshift_r(wf_nx, wf_lo, fsh);                   \
+        const uint32_t nqb = __brev(__funnelshift_r(wb_hi, wb_nx, bsh));           \
+        wf_lo = wf_nx; wb_hi = wb_nx;                                              \
         --pf; ++pb;                                                                \
-        nfA = pf[0]; nbA = pb[1];                                                  \
-        if (PAIR) { nfB = pf[dW]; nbB = pb[1 + dW]; }                              \
-        const uint32_t qfA = __funnelshift_r(flA, fhA, fsh);                       \
-        const uint32_t qfB = PAIR ? __funnelshift_r(flB, fhB, fsh) : 0u;           \
-        fhA = flA; fhB = flB;                                                      \
-        const uint32_t qbA = __brev(__funnelshift_r(blA, bhA, bsh));               \
-        const uint32_t qbB = PAIR ? __brev(__funnelshift_r(blB, bhB, bsh)) : 0u;   \
-        blA = bhA; blB = bhB;
+        wf_nx = pf[-1]; wb_nx = pb[WS + 1];                                        \
+        _Pragma("unroll") for (int j = WS - 1; j > 0; --j) qf[j] = qf[j - 1];      \
+        _Pragma("unroll") for (int j = 0; j < WS - 1; ++j) qb[j] = qb[j + 1];      \
+        qf[0] = nqf; qb[WS - 1] = nqb;                                             \
+    }
 #define D2P_STEP(GUARD, D)                                                         \
     {                                                                              \
         uint32_t rsel = ((D) & 1) ? L.rlo : L.rhi;                                 \
@@ -486,21 +495,19 @@ __device__ __forceinline__ void lutfir_pair(const KParams& P, const LaneLut& L, 
             rsel = live ? rsel : 0u;                                               \
             t = live ? tp : tp + (uint32_t)L.dz;                                   \
         }                                                                          \
-        const uint32_t afA = (D) < 2 ? __dp2a_hi(rsel, qfA, t) : __dp2a_lo(rsel, qfA, t);   \
-        const uint32_t abA = (D) < 2 ? __dp2a_hi(rsel, qbA, t) : __dp2a_lo(rsel, qbA, t);   \
-        const double tfA = lds_f64<8 * (D)>(afA), tbA = lds_f64<8 * (D)>(abA);     \
-        accA = __dadd_rn(__dadd_rn(accA, tfA), tbA);                               \
-        if (PAIR) {                                                                \
-            const uint32_t afB = (D) < 2 ? __dp2a_hi(rsel, qfB, t) : __dp2a_lo(rsel, qfB, t);   \
-            const uint32_t abB = (D) < 2 ? __dp2a_hi(rsel, qbB, t) : __dp2a_lo(rsel, qbB, t);   \
-            const double tfB = lds_f64<8 * (D)>(afB), tbB = lds_f64<8 * (D)>(abB); \
-            accB = __dadd_rn(__dadd_rn(accB, tfB), tbB);                           \
+        double tf[F], tb[F];                                                       \
+        _Pragma("unroll") for (int f = 0; f < F; ++f) {                            \
+            const uint32_t af = (D) < 2 ? __dp2a_hi(rsel, qf[f * DW], t) : __dp2a_lo(rsel, qf[f * DW], t);   \
+            const uint32_t ab = (D) < 2 ? __dp2a_hi(rsel, qb[f * DW], t) : __dp2a_lo(rsel, qb[f * DW], t);   \
+            tf[f] = lds_f64<8 * (D)>(af); tb[f] = lds_f64<8 * (D)>(ab);            \
         }                                                                          \
+        _Pragma("unroll") for (int f = 0; f < F; ++f)                              \
+            acc[f] = __dadd_rn(__dadd_rn(acc[f], tf[f]), tb[f]);                   \
     }
 #define D2P_GROUP(GUARD)                                                           \
     {                                                                              \
-        D2P_FETCH()                                                                \
         D2P_STEP(GUARD, 0) D2P_STEP(GUARD, 1) D2P_STEP(GUARD, 2) D2P_STEP(GUARD, 3) \
+        D2P_ADVANCE()                                                              \
         tp += 32; i0 += 4;                                                         \
     }
     for (; g < gp_lo; ++g) D2P_GROUP(true)
@@ -509,7 +516,6 @@ __device__ __forceinline__ void lutfir_pair(const KParams& P, const LaneLut& L, 
     for (; g < ng - 1; ++g) D2P_GROUP(true)
     if (g < ng) {
         // last group: steps beyond nt + K - 1 are idle for every lane and are not issued at all
-        D2P_FETCH()
         const int ls = P.last_steps;
         D2P_STEP(true, 0)
         if (ls > 1) D2P_STEP(true, 1)
@@ -518,11 +524,12 @@ __device__ __forceinline__ void lutfir_pair(const KParams& P, const LaneLut& L, 
     }
 #undef D2P_GROUP
 #undef D2P_STEP
-#undef D2P_FETCH
-    yA = accA; yB = accB;
+#undef D2P_ADVANCE
+#pragma unroll
+    for (int f = 0; f < F; ++f) y[f] = acc[f];
 }
 
-template <int WM, int DITH>
+template <int WM, int DITH, int F, int DW>
 __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_constant__ KParams P) {
     extern __shared__ __align__(16) unsigned char smem[];
     // [zero region | LUT | 2 input tiles | 2 output stages]
@@ -589,74 +596,36 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
             const TileInfo t = hdr[bsel];
             const unsigned char* tiles = inbuf + (size_t)bsel * P.in_buf_bytes;
             unsigned char* ostage = obuf + (size_t)bsel * P.ostage_bytes;
-            const int items = P.C << P.tf_shift;                  // item = channel * TF + frame-in-tile
             const int bpo = P.bpo;
             em.set_job(*t.J);
-            if (t.nf == P.TF && P.TF >= 2 * nc) {
-                // Full tile whose channels split into whole passes of 2*nc frames: thread tid runs frames
-                // A = pass*2nc + tid and B = A + nc of every channel.  From one pass to the next both byte streams
-                // move by a whole number of words, so the cursor is set up once per tile and only advanced.
-                FrameCursor K = frame_cursor(reinterpret_cast<const uint32_t*>(tiles), (tid + 1) * bpo - 1 + t.jr_base, c, P.nt);
-                const int dW = (nc * bpo) >> 2, passW = (2 * nc * bpo) >> 2, chW = P.tile_stride >> 2;
-                const int npass = P.TF / (2 * nc);
-                for (int ch = 0; ch < P.C; ++ch) {
-                    FrameCursor Kp = K;
-                    for (int ps = 0, fl = tid; ps < npass; ++ps, fl += 2 * nc) {
-                        double yA, yB;
-                        lutfir_pair<true>(P, LL, Kp, dW, tp0, yA, yB);
-                        if (WM == 1) {                              // both dither / rounding chains side by side
-                            const int vA = em.quant(P, ch, t.f0 + fl, yA), vB = em.quant(P, ch, t.f0 + fl + nc, yB);
-                            em.put(P, *t.J, ostage, ch, t.f0 + fl, fl, vA);
-                            em.put(P, *t.J, ostage, ch, t.f0 + fl + nc, fl + nc, vB);
-                        } else {
-                            em.emit(P, *t.J, ostage, ch, t.f0 + fl, fl, yA);
-                            em.emit(P, *t.J, ostage, ch, t.f0 + fl + nc, fl + nc, yB);
-                        }
-                        Kp.pf += passW; Kp.pb += passW;
+            // One item = one frame set: slot s of channel ch holds the frames fl0 + f*fpw, f < F, with
+            // fl0 = (s / fpw) * F * fpw + s % fpw  (fpw = frames per 32-bit word of the stream, 1 unless bpo < 4).
+            const int items = P.C << P.sl_shift;
+            const int fs = P.fpw_shift, fpw = 1 << fs;
+            for (int it = tid; it < items; it += nc) {
+                const int ch = it >> P.sl_shift, slot = it & ((1 << P.sl_shift) - 1);
+                // warp-uniform: the first lane of the warp holds the warp's earliest frame
+                if (((((slot & ~31) >> fs) * F) << fs) >= t.nf) continue;
+                const int fl0 = (((slot >> fs) * F) << fs) + (slot & (fpw - 1));
+                const uint32_t* tw = reinterpret_cast<const uint32_t*>(tiles + (size_t)ch * P.tile_stride);
+                double y[F];
+                lutfir_set<F, DW>(P, LL, tw, (fl0 + 1) * bpo - 1 + t.jr_base, tp0, y);
+                if (WM == 1) {                                  // the dither / rounding chains of the set side by side
+                    int v[F];
+#pragma unroll
+                    for (int f = 0; f < F; ++f) v[f] = em.quant(P, ch, t.f0 + fl0 + (f << fs), y[f]);
+#pragma unroll
+                    for (int f = 0; f < F; ++f) {
+                        const int fl = fl0 + (f << fs);
+                        if (fl < t.nf) em.put(P, *t.J, ostage, ch, t.f0 + fl, fl, v[f]);
                     }
-                    K.pf += chW; K.pb += chW;
-                }
-            } else
-            // Passes over the tile's items.  While at least 2*nc items remain, every consumer thread runs two
-            // frames in lockstep (A = base + tid, B = A + nc); a remainder of more than nc items is split into
-            // two halves the same way; up to nc items run one frame per thread.
-            for (int base = 0; base < items;) {
-                const int rem = items - base;
-                const bool pair = rem > nc;
-                const int ps = rem >= 2 * nc ? nc : (pair ? (((rem + 1) >> 1) + 31) & ~31 : rem);
-                if (tid < ps) {
-                    const int it = base + tid;
-                    const int ch = it >> P.tf_shift, fl = it & (P.TF - 1);
-                    const uint32_t* tw = reinterpret_cast<const uint32_t*>(tiles + (size_t)ch * P.tile_stride);
-                    const int jr = (fl + 1) * bpo - 1 + t.jr_base;
-                    const FrameCursor K = frame_cursor(tw, jr, c, P.nt);
-                    if (pair) {
-                        const int itB = it + ps;
-                        const bool hasB = itB < items;
-                        const int chB = itB >> P.tf_shift, flB = itB & (P.TF - 1);
-                        // warp-uniform: lanes are 32 consecutive frames of an aligned group
-                        if ((fl & ~31) < t.nf || (hasB && (flB & ~31) < t.nf)) {
-                            // B's bytes sit a fixed, word-aligned distance from A's (ps and TF are multiples of 32)
-                            const int dW = hasB ? ((chB - ch) * P.tile_stride + (flB - fl) * bpo) >> 2 : 0;
-                            double yA, yB;
-                            lutfir_pair<true>(P, LL, K, dW, tp0, yA, yB);
-                            const bool okA = fl < t.nf, okB = hasB && flB < t.nf;
-                            if (WM == 1 && okA && okB) {
-                                const int vA = em.quant(P, ch, t.f0 + fl, yA), vB = em.quant(P, chB, t.f0 + flB, yB);
-                                em.put(P, *t.J, ostage, ch, t.f0 + fl, fl, vA);
-                                em.put(P, *t.J, ostage, chB, t.f0 + flB, flB, vB);
-                            } else {
-                                if (okA) em.emit(P, *t.J, ostage, ch, t.f0 + fl, fl, yA);
-                                if (okB) em.emit(P, *t.J, ostage, chB, t.f0 + flB, flB, yB);
-                            }
-                        }
-                    } else if ((fl & ~31) < t.nf) {
-                        double yA, yB;
-                        lutfir_pair<false>(P, LL, K, 0, tp0, yA, yB);
-                        if (fl < t.nf) em.emit(P, *t.J, ostage, ch, t.f0 + fl, fl, yA);
+                } else {
+#pragma unroll
+                    for (int f = 0; f < F; ++f) {
+                        const int fl = fl0 + (f << fs);
+                        if (fl < t.nf) em.emit(P, *t.J, ostage, ch, t.f0 + fl, fl, y[f]);
                     }
                 }
-                base += pair ? 2 * ps : ps;
             }
         }
         have_prev = true;
@@ -1017,10 +986,26 @@ __global__ void __launch_bounds__(256) fpd_kernel(const __grid_constant__ KParam
 // ------------------------------------------------------------------------------------------------
 const char* kernel_name(bool lm) { return lm ? "d2p::lm_kernel" : "d2p::lutfir_kernel"; }
 
-// variant: 0 = lm_kernel, 1 = lutfir generic writer, 2/3/4 = lutfir fast 3-byte-LE writer with dither X/T/R
+// variant: 10..25 = lm_kernel instantiations; 100 + 10*shape + writer = lutfir_kernel, with
+//   shape  0: sets of 3 frames one word apart (bpo <= 4), 1: 3 frames two words apart (bpo 8), 2: 2 frames four words apart (bpo 16)
+//   writer 1: generic, 2/3/4: fast 3-byte-LE writer with dither X/T/R
+template <int F, int DW>
+static const void* lutfir_fn(int writer) {
+    switch (writer) {
+    case 2: return (const void*)lutfir_kernel<1, 0, F, DW>;
+    case 3: return (const void*)lutfir_kernel<1, 'T', F, DW>;
+    case 4: return (const void*)lutfir_kernel<1, 'R', F, DW>;
+    default: return (const void*)lutfir_kernel<0, 0, F, DW>;
+    }
+}
 static const void* kernel_fn(int variant) {
+    if (variant >= 100) {
+        const int shape = (variant - 100) / 10, writer = (variant - 100) % 10;
+        if (shape == 1) return lutfir_fn<3, 2>(writer);
+        if (shape == 2) return lutfir_fn<2, 4>(writer);
+        return lutfir_fn<3, 1>(writer);
+    }
     switch (variant) {
-    case 0: case 15: return (const void*)lm_kernel<5, kLmConsumersSmall>;
     case 11: return (const void*)lm_kernel<1, kLmConsumersSmall>;
     case 12: return (const void*)lm_kernel<2, kLmConsumersSmall>;
     case 13: return (const void*)lm_kernel<3, kLmConsumersSmall>;
@@ -1030,21 +1015,24 @@ static const void* kernel_fn(int variant) {
     case 23: return (const void*)lm_kernel<3, kLmConsumers>;
     case 24: return (const void*)lm_kernel<4, kLmConsumers>;
     case 25: return (const void*)lm_kernel<5, kLmConsumers>;
-    case 2: return (const void*)lutfir_kernel<1, 0>;
-    case 3: return (const void*)lutfir_kernel<1, 'T'>;
-    case 4: return (const void*)lutfir_kernel<1, 'R'>;
-    default: return (const void*)lutfir_kernel<0, 0>;
+    default: return (const void*)lm_kernel<5, kLmConsumersSmall>;
     }
+}
+
+void lutfir_set_shape(int bpo, int* F, int* DW) {
+    *DW = bpo <= 4 ? 1 : bpo / 4;
+    *F = *DW >= 4 ? 2 : 3;
 }
 
 int kernel_variant(const KParams& P, bool lm, bool fast_writer_ok) {
     if (lm) return (P.lm_cons == kLmConsumers ? 20 : 10) + (P.gmax < 1 ? 1 : (P.gmax > 5 ? 5 : P.gmax));
-    if (!fast_writer_ok) return 1;
-    return P.dither == 'T' ? 3 : (P.dither == 'R' ? 4 : 2);
+    const int shape = P.setDW == 1 ? 0 : (P.setDW == 2 ? 1 : 2);
+    const int writer = !fast_writer_ok ? 1 : (P.dither == 'T' ? 3 : (P.dither == 'R' ? 4 : 2));
+    return 100 + 10 * shape + writer;
 }
 
 static cudaError_t ensure_smem_attr(int variant) {
-    static bool attr_done[32][64] = {};
+    static bool attr_done[160][64] = {};
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
@@ -1058,7 +1046,7 @@ static cudaError_t ensure_smem_attr(int variant) {
 }
 
 int max_ctas_per_sm(bool lm, int threads, size_t smem) {
-    const int variant = lm ? (threads > kLmConsumersSmall + kLmProducers ? 25 : 15) : 1;
+    const int variant = lm ? (threads > kLmConsumersSmall + kLmProducers ? 25 : 15) : 101;
     if (ensure_smem_attr(variant) != cudaSuccess) return 0;
     int n = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel_fn(variant), threads, smem) != cudaSuccess) { cudaGetLastError(); return 0; }

@@ -23,10 +23,10 @@ static const int kLmProducers = 64;          // extra threads of lm_kernel (same
 static const int kLmConsumersSmall = 448;
 static const int kLmConsumers = 896;
 static const int kLmThreads = kLmConsumers + kLmProducers;
-static const int kLutPad = 128;              // legacy pad constant (lm_kernel does not use it)
 static const int kMaxSmem = 227 * 1024;      // opt-in dynamic shared memory per CTA on sm_100a
 
 const char* kernel_name(bool lm);
+void lutfir_set_shape(int bpo, int* F, int* DW);          // frames per lane set / word distance the kernels are built for
 int max_ctas_per_sm(bool lm, int threads, size_t smem);   // occupancy of the kernel at this geometry (0 on error)
 int kernel_variant(const KParams& P, bool lm, bool fast_writer_ok);   // which instantiation a launch uses
 cudaError_t launch_fpd(const KParams& P, cudaStream_t stream);     // per-sample xorshift32 states for dither F
