@@ -36,6 +36,22 @@ def fixtures():
 
 
 @pytest.fixture(scope="session")
+def ref_files(tmp_path_factory):
+    """The reference's DSD fixtures, whole (tests/golden/ref_fixtures.tar.xz, made by make_ref_fixtures.sh):
+    relative path -> absolute path of the unpacked file."""
+    import tarfile
+    root = tmp_path_factory.mktemp("ref_fixtures")
+    with tarfile.open(os.path.join(HERE, "golden", "ref_fixtures.tar.xz"), "r:xz") as tf:
+        tf.extractall(root, filter="data")
+    out = {}
+    for d, _, files in os.walk(root):
+        for f in files:
+            full = os.path.join(d, f)
+            out[os.path.relpath(full, root)] = full
+    return out
+
+
+@pytest.fixture(scope="session")
 def golden_digests():
     return json.load(open(os.path.join(HERE, "golden", "golden_digests.json")))
 
