@@ -106,9 +106,12 @@ def test_whole_fixture_dithers_exact_and_within_one_lsb(ref_files, rel, dither):
         kw = dict(out_rate=out_rate, bits=bits, dither_seed=0xD17 + bits, **fmt)
         ref = orclib.convert(raw, want_f64=False, dither=dither, stdout_mode=False, **kw)
         clean = orclib.convert(raw, want_f64=False, dither="X", stdout_mode=False, **kw)
-        pcm, frames, _ = d2p.convert_host(d2p.make_config(dither=dither, out_format=_capi.OUT_PLANAR_32, **kw), raw)
-        got = pcm.view(np.float32 if bits == 32 else np.int32).reshape(fmt["channels"], -1)
-        assert frames == ref.frames[0]
+        conv = d2p.Converter(d2p.make_config(dither=dither, out_format=_capi.OUT_PLANAR_32, **kw))
+        conv.push(raw)
+        conv.finish()
+        got = conv.pull()                                     # [channels, frames] int32 / float32 (AudioFile samples)
+        conv.close()
+        assert got.shape[1] == ref.frames[0]
         assert np.array_equal(got, ref.planar), (rel, kw)
         if bits == 32:      # one step of the 2^(e-24)-scaled noise: a few f32 ulps of the sample
             assert np.all(np.abs(got.astype(np.float64) - clean.planar) <= 4 * np.spacing(np.abs(clean.planar).astype(np.float32)) + 1e-30)
