@@ -37,6 +37,36 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+// ---- TMA bulk copies (cp.async.bulk, SASS: UBLKCP) completed on an mbarrier (SYNCS) ------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                     : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    } while (!done);
+}
+// global -> shared, 16-byte aligned on both sides, size a multiple of 16; completion is counted on `bar`
+__device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+// shared -> global, same alignment rules; tracked by the issuing thread's bulk async-group
+__device__ __forceinline__ void tma_store_1d(void* gdst, const void* smem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" :: "l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// generic-proxy writes to shared memory made visible to the async proxy (before a bulk store reads them)
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
 __device__ __forceinline__ uint32_t bitrev_each_byte(uint32_t w) {   // MSB-first -> LSB-first
     return __byte_perm(__brev(w), 0, 0x0123);
 }
@@ -155,9 +185,13 @@ __device__ void stage_interleaved(const KParams& P, const DevJob& J, unsigned ch
 // into shared memory straight from the container layout (de-interleave / de-block / bit-reverse fused
 // into the load).  Positions outside [0, end_q) read as 0.  s_lo and nbytes are multiples of 16.
 // ------------------------------------------------------------------------------------------------
+// bar != nullptr: the untransformed interior of a DSF-style payload is moved by TMA bulk copies (one per channel and
+// 4096-byte block run) that complete on *bar; thread 0 arms the barrier with the byte count of this tile (0 if the
+// layout needs the register path), so a waiter on *bar never hangs.  bar == nullptr: 16-byte cp.async copies.
 __device__ void stage_input(const KParams& P, const DevJob& J, unsigned char* tiles, long long s_lo, int nbytes,
-                            int tid, int nthr) {
+                            int tid, int nthr, unsigned long long* bar = nullptr) {
     const int C = P.C;
+    if (P.layout != 'P' && bar && tid == 0) mbar_arrive_expect_tx(bar, 0u);
     if (P.layout == 'P') {
         const int nvec = nbytes >> 4;
         const bool fast = ((P.block_size & 15) == 0) && ((((uintptr_t)J.in) & 15) == 0) && ((J.base_q & 15) == 0);
@@ -172,7 +206,19 @@ __device__ void stage_input(const KParams& P, const DevJob& J, unsigned char* ti
             a = a < 0 ? 0 : (a > nvec ? nvec : a);
             b = b < a ? a : (b > nvec ? nvec : b);
             i_lo = (int)a; i_hi = (int)b;
-            if (i_hi > i_lo) {
+            if (bar && i_hi > i_lo) {
+                const int nint = i_hi - i_lo, bs = P.block_shift;
+                const long long qr0 = s_lo + 16LL * i_lo - J.base_q;
+                const long long blk0 = qr0 >> bs;
+                const int w0 = (int)(qr0 & (P.block_size - 1)), w1 = w0 + 16 * nint;
+                const int nruns = ((w1 - 1) >> bs) + 1;               // block runs the interior touches
+                for (int it = tid; it < nruns * C; it += nthr) {
+                    const int c = it / nruns, k = it - c * nruns;
+                    const int lo = k == 0 ? w0 : (k << bs), hi = w1 < ((k + 1) << bs) ? w1 : ((k + 1) << bs);
+                    tma_load_1d(tiles + (size_t)c * P.tile_stride + 16 * i_lo + (lo - w0),
+                                J.in + (((blk0 + k) * C + c) << bs) + (lo - (k << bs)), (uint32_t)(hi - lo), bar);
+                }
+            } else if (i_hi > i_lo) {
                 const long long qr0 = s_lo + 16LL * i_lo - J.base_q;
                 const long long blk0 = qr0 >> P.block_shift;
                 const int w0 = (int)(qr0 & (P.block_size - 1)), mask = P.block_size - 1;
@@ -186,6 +232,7 @@ __device__ void stage_input(const KParams& P, const DevJob& J, unsigned char* ti
                 }
             }
         }
+        if (bar && tid == 0) mbar_arrive_expect_tx(bar, (uint32_t)((i_hi - i_lo) * 16 * C));
         const int nedge = nvec - (i_hi - i_lo);
         for (int v = tid; v < nedge * C; v += nthr) {
             const int c = v / nedge, e = v - c * nedge;
@@ -361,6 +408,15 @@ __device__ void copy_out(unsigned char* dst, const unsigned char* src, int nbyte
     } else {
         for (int i = tid; i < nbytes; i += nthr) dst[i] = src[i];
     }
+}
+
+// The packed tile is one contiguous run of the output stream: one TMA bulk store (shared -> global) issued by thread 0
+// for the 16-byte multiple of it when the destination is 16-byte aligned; the other threads copy what is left.
+__device__ void copy_out_tma(unsigned char* dst, const unsigned char* src, int nbytes, int tid, int nthr) {
+    if ((((uintptr_t)dst) & 15) != 0 || nbytes < 16) { copy_out(dst, src, nbytes, tid, nthr); return; }
+    const int nb16 = nbytes & ~15;
+    if (tid == 0) { tma_store_1d(dst, src, (uint32_t)nb16); tma_store_commit(); }
+    for (int i = nb16 + tid; i < nbytes; i += nthr) dst[i] = src[i];
 }
 
 __device__ __forceinline__ void load_lut(double* dst, const double* __restrict__ src, int n) {
@@ -563,14 +619,21 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
     // tile headers (job look-up, 64-bit position arithmetic) are worked out by the producer warps only, one tile
     // ahead, and handed to the consumers through shared memory
     __shared__ TileInfo hdr[2];
+    __shared__ __align__(8) unsigned long long full[2];            // mbarriers: TMA bytes of input buffer 0 / 1 have landed
+    if (tid == 0) {
+        mbar_init(&full[0], 1); mbar_init(&full[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
     unsigned int tile = blockIdx.x;
     TileInfo cur, prev;
     cur.J = nullptr; prev.J = nullptr;
     if (tile < P.total_tiles && producer) {
         cur = lutfir_tile(P, tile);
         if (ptid == 0) hdr[0] = cur;
-        stage_input(P, *cur.J, inbuf, cur.s_lo, cur.nbytes, ptid, np);
+        stage_input(P, *cur.J, inbuf, cur.s_lo, cur.nbytes, ptid, np, &full[0]);
         cp_async_wait_all();
+        mbar_wait(&full[0], 0u);
     }
     __syncthreads();
 
@@ -585,12 +648,14 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
             if (nxt < P.total_tiles) {
                 tn = lutfir_tile(P, nxt);
                 if (ptid == 0) hdr[bsel ^ 1] = tn;
-                stage_input(P, *tn.J, inbuf + (size_t)(bsel ^ 1) * P.in_buf_bytes, tn.s_lo, tn.nbytes, ptid, np);
+                stage_input(P, *tn.J, inbuf + (size_t)(bsel ^ 1) * P.in_buf_bytes, tn.s_lo, tn.nbytes, ptid, np, &full[bsel ^ 1]);
             }
             if (have_prev && staged_out)
-                copy_out(prev.J->out + (size_t)(prev.f0 - prev.J->f_begin) * fb, obuf + (size_t)(bsel ^ 1) * P.ostage_bytes,
-                         (int)(prev.nf * fb), ptid, np);
+                copy_out_tma(prev.J->out + (size_t)(prev.f0 - prev.J->f_begin) * fb, obuf + (size_t)(bsel ^ 1) * P.ostage_bytes,
+                             (int)(prev.nf * fb), ptid, np);
             cp_async_wait_all();
+            if (nxt < P.total_tiles) mbar_wait(&full[bsel ^ 1], (uint32_t)(((j + 1) >> 1) & 1));   // that buffer's ((j+1)/2)-th fill
+            if (ptid == 0) tma_store_wait_read();                  // the output stage may be rewritten after the barrier
             prev = cur; cur = tn;
         } else {
             const TileInfo t = hdr[bsel];
@@ -627,13 +692,16 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
                     }
                 }
             }
+            if (staged_out) fence_proxy_async();                   // this thread's packed PCM -> visible to the bulk store
         }
         have_prev = true;
         __syncthreads();
     }
-    if (producer && have_prev && staged_out)
-        copy_out(prev.J->out + (size_t)(prev.f0 - prev.J->f_begin) * fb, obuf + (size_t)((j - 1) & 1) * P.ostage_bytes,
-                 (int)(prev.nf * fb), ptid, np);
+    if (producer && have_prev && staged_out) {
+        copy_out_tma(prev.J->out + (size_t)(prev.f0 - prev.J->f_begin) * fb, obuf + (size_t)((j - 1) & 1) * P.ostage_bytes,
+                     (int)(prev.nf * fb), ptid, np);
+        if (ptid == 0) tma_store_wait_all();
+    }
     if (!producer) em.flush(P);
 }
 
