@@ -499,18 +499,27 @@ struct LaneLut { uint32_t rlo, rhi; int dz, c; };
 //   mirrored half: step u reads byte jr - (2nt-1) - c + u
 // jr: tile-relative index of the newest byte of the set's first frame; c: the lane's skew.
 template <int F, int DW>
-__device__ __forceinline__ void lutfir_set(const KParams& P, const LaneLut& L, const uint32_t* tw, int jr,
-                                           uint32_t tp0, double (&y)[F]) {
-    constexpr int WS = (F - 1) * DW + 1;          // window: frame f reads entry f*DW
-    const int nt = P.nt;
-    const int c = L.c;
-    const int a = jr + c - 3, b = jr - (2 * nt - 1) - c;
-    const uint32_t* pf = tw + (a >> 2);
-    const uint32_t* pb = tw + (b >> 2);
-    const int fsh = (a & 3) * 8, bsh = (b & 3) * 8;
-    uint32_t qf[WS], qb[WS];                      // qf[j]: forward group of window slot j;  qb[j]: mirrored, bit-reversed
+struct FrameSet {
+    static constexpr int WS = (F - 1) * DW + 1;   // window: frame f reads logical entry f*DW
+    // The windows are ring buffers in registers.  After n advances (rotation ROT = n mod WS) logical entry j of the
+    // forward window is qf[(j - ROT) mod WS] and of the mirrored window qb[(j + ROT) mod WS]: an advance overwrites
+    // exactly the entry that drops out, nothing moves.  ROT is a compile-time constant of every group, so the main
+    // loop is unrolled WS groups deep and all indexing stays static.
+    uint32_t qf[WS], qb[WS];                      // forward 4-byte groups; mirrored ones, bit-reversed
     uint32_t wf_lo, wf_nx, wb_hi, wb_nx;          // raw tile words at the window edges and the prefetched next ones
-    {
+    const uint32_t* pf;
+    const uint32_t* pb;
+    int fsh, bsh;
+    double acc[F];
+    uint32_t tp, rlo, rhi, dz;
+    int i0, nt;
+
+    __device__ __forceinline__ void init(const KParams& P, const LaneLut& L, const uint32_t* tw, int jr, uint32_t tp0) {
+        nt = P.nt;
+        const int c = L.c;
+        const int a = jr + c - 3, b = jr - (2 * nt - 1) - c;
+        pf = tw + (a >> 2); pb = tw + (b >> 2);
+        fsh = (a & 3) * 8; bsh = (b & 3) * 8;
         uint32_t w[WS + 1];
 #pragma unroll
         for (int j = 0; j <= WS; ++j) w[j] = pf[j];
@@ -522,67 +531,99 @@ __device__ __forceinline__ void lutfir_set(const KParams& P, const LaneLut& L, c
 #pragma unroll
         for (int j = 0; j < WS; ++j) qb[j] = __brev(__funnelshift_r(w[j], w[j + 1], bsh));
         wb_hi = w[WS]; wb_nx = pb[WS + 1];
-    }
-    double acc[F];
 #pragma unroll
-    for (int f = 0; f < F; ++f) acc[f] = 0.0;
-    uint32_t tp = tp0;
-    int i0 = -c;
-    const int gp_lo = P.gp_lo, gp_hi = P.gp_hi, ng = P.ngroups;
-    int g = 0;
+        for (int f = 0; f < F; ++f) acc[f] = 0.0;
+        tp = tp0; rlo = L.rlo; rhi = L.rhi; dz = (uint32_t)L.dz;
+        i0 = -c;
+    }
+
+    template <bool GUARD, int D, int ROT>
+    __device__ __forceinline__ void step() {
+        uint32_t rsel = (D & 1) ? rlo : rhi;
+        uint32_t t = tp;
+        if (GUARD) {
+            const bool live = (unsigned)(i0 + D) < (unsigned)nt;
+            rsel = live ? rsel : 0u;
+            t = live ? tp : tp + dz;
+        }
+        double tf[F], tb[F];
+#pragma unroll
+        for (int f = 0; f < F; ++f) {
+            const uint32_t vf = qf[(f * DW - ROT + WS) % WS], vb = qb[(f * DW + ROT) % WS];
+            const uint32_t af = D < 2 ? __dp2a_hi(rsel, vf, t) : __dp2a_lo(rsel, vf, t);
+            const uint32_t ab = D < 2 ? __dp2a_hi(rsel, vb, t) : __dp2a_lo(rsel, vb, t);
+            tf[f] = lds_f64<8 * D>(af); tb[f] = lds_f64<8 * D>(ab);
+        }
+#pragma unroll
+        for (int f = 0; f < F; ++f) acc[f] = __dadd_rn(__dadd_rn(acc[f], tf[f]), tb[f]);
+    }
+
     // the words of the NEXT group are fetched one group ahead, so that a group never waits on its own tile loads
-#define D2P_ADVANCE()                                                              \
-    {                                                                              \
-        const uint32_t nqf = __funnelshift_r(wf_nx, wf_lo, fsh);                   \
-        const uint32_t nqb = __brev(__funnelshift_r(wb_hi, wb_nx, bsh));           \
-        wf_lo = wf_nx; wb_hi = wb_nx;                                              \
-        --pf; ++pb;                                                                \
-        wf_nx = pf[-1]; wb_nx = pb[WS + 1];                                        \
-        _Pragma("unroll") for (int j = WS - 1; j > 0; --j) qf[j] = qf[j - 1];      \
-        _Pragma("unroll") for (int j = 0; j < WS - 1; ++j) qb[j] = qb[j + 1];      \
-        qf[0] = nqf; qb[WS - 1] = nqb;                                             \
+    template <int ROT>
+    __device__ __forceinline__ void advance() {
+        const uint32_t nqf = __funnelshift_r(wf_nx, wf_lo, fsh);
+        const uint32_t nqb = __brev(__funnelshift_r(wb_hi, wb_nx, bsh));
+        wf_lo = wf_nx; wb_hi = wb_nx;
+        --pf; ++pb;
+        wf_nx = pf[-1]; wb_nx = pb[WS + 1];
+        qf[(WS - 1 - ROT + WS) % WS] = nqf;       // becomes logical entry 0 at rotation ROT + 1
+        qb[ROT % WS] = nqb;                       // becomes logical entry WS - 1 at rotation ROT + 1
+        tp += 32; i0 += 4;
     }
-#define D2P_STEP(GUARD, D)                                                         \
-    {                                                                              \
-        uint32_t rsel = ((D) & 1) ? L.rlo : L.rhi;                                 \
-        uint32_t t = tp;                                                           \
-        if (GUARD) {                                                               \
-            const bool live = (unsigned)(i0 + (D)) < (unsigned)nt;                 \
-            rsel = live ? rsel : 0u;                                               \
-            t = live ? tp : tp + (uint32_t)L.dz;                                   \
-        }                                                                          \
-        double tf[F], tb[F];                                                       \
-        _Pragma("unroll") for (int f = 0; f < F; ++f) {                            \
-            const uint32_t af = (D) < 2 ? __dp2a_hi(rsel, qf[f * DW], t) : __dp2a_lo(rsel, qf[f * DW], t);   \
-            const uint32_t ab = (D) < 2 ? __dp2a_hi(rsel, qb[f * DW], t) : __dp2a_lo(rsel, qb[f * DW], t);   \
-            tf[f] = lds_f64<8 * (D)>(af); tb[f] = lds_f64<8 * (D)>(ab);            \
-        }                                                                          \
-        _Pragma("unroll") for (int f = 0; f < F; ++f)                              \
-            acc[f] = __dadd_rn(__dadd_rn(acc[f], tf[f]), tb[f]);                   \
+
+    template <bool GUARD, int ROT>
+    __device__ __forceinline__ void group() {
+        step<GUARD, 0, ROT>(); step<GUARD, 1, ROT>(); step<GUARD, 2, ROT>(); step<GUARD, 3, ROT>();
+        advance<ROT>();
     }
-#define D2P_GROUP(GUARD)                                                           \
-    {                                                                              \
-        D2P_STEP(GUARD, 0) D2P_STEP(GUARD, 1) D2P_STEP(GUARD, 2) D2P_STEP(GUARD, 3) \
-        D2P_ADVANCE()                                                              \
-        tp += 32; i0 += 4;                                                         \
+    // WS - ROT groups starting at rotation ROT (ends at rotation 0)
+    template <bool GUARD, int ROT>
+    __device__ __forceinline__ void groups_to_wrap() {
+        group<GUARD, ROT>();
+        if constexpr (ROT + 1 < WS) groups_to_wrap<GUARD, ROT + 1>();
     }
-    for (; g < gp_lo; ++g) D2P_GROUP(true)
-#pragma unroll 1
-    for (; g < gp_hi; ++g) D2P_GROUP(false)
-    for (; g < ng - 1; ++g) D2P_GROUP(true)
-    if (g < ng) {
-        // last group: steps beyond nt + K - 1 are idle for every lane and are not issued at all
-        const int ls = P.last_steps;
-        D2P_STEP(true, 0)
-        if (ls > 1) D2P_STEP(true, 1)
-        if (ls > 2) D2P_STEP(true, 2)
-        if (ls > 3) D2P_STEP(true, 3)
-    }
-#undef D2P_GROUP
-#undef D2P_STEP
-#undef D2P_ADVANCE
+    // n < WS groups starting at rotation 0, then the entries are moved back to rotation 0
+    template <bool GUARD>
+    __device__ __forceinline__ void groups_few(int n) {
+        for (int k = 0; k < n; ++k) {
+            group<GUARD, 0>();
+            // rotation 1 -> 0: logical j sits at qf[(j - 1) mod WS], qb[(j + 1) mod WS]
+            const uint32_t lf = qf[WS - 1], lb = qb[0];
 #pragma unroll
-    for (int f = 0; f < F; ++f) y[f] = acc[f];
+            for (int j = WS - 1; j > 0; --j) qf[j] = qf[j - 1];
+#pragma unroll
+            for (int j = 0; j < WS - 1; ++j) qb[j] = qb[j + 1];
+            qf[0] = lf; qb[WS - 1] = lb;
+        }
+    }
+
+    __device__ __forceinline__ void run(const KParams& P, double (&y)[F]) {
+        const int gp_lo = P.gp_lo, gp_hi = P.gp_hi, ng = P.ngroups;
+        int g = 0;
+        groups_few<true>(gp_lo); g = gp_lo;
+#pragma unroll 1
+        for (; g + WS <= gp_hi; g += WS) groups_to_wrap<false, 0>();
+        groups_few<false>(gp_hi - g); g = gp_hi;
+        if (ng - 1 > g) { groups_few<true>(ng - 1 - g); g = ng - 1; }
+        if (g < ng) {
+            // last group: steps beyond nt + K - 1 are idle for every lane and are not issued at all
+            const int ls = P.last_steps;
+            step<true, 0, 0>();
+            if (ls > 1) step<true, 1, 0>();
+            if (ls > 2) step<true, 2, 0>();
+            if (ls > 3) step<true, 3, 0>();
+        }
+#pragma unroll
+        for (int f = 0; f < F; ++f) y[f] = acc[f];
+    }
+};
+
+template <int F, int DW>
+__device__ __forceinline__ void lutfir_set(const KParams& P, const LaneLut& L, const uint32_t* tw, int jr,
+                                           uint32_t tp0, double (&y)[F]) {
+    FrameSet<F, DW> S;
+    S.init(P, L, tw, jr, tp0);
+    S.run(P, y);
 }
 
 template <int WM, int DITH, int F, int DW>
