@@ -229,6 +229,23 @@ class Batch:
                                                        C.byref(frames)))
         return int(frames.value)
 
+    def job_stats(self, njobs, stream=0):
+        """Per job of the most recent run: (peak_abs list, clipped_samples list) -- dsd_levels' one peak per file."""
+        clipped = (C.c_int64 * max(njobs, 1))()
+        peak = (C.c_double * max(njobs, 1))()
+        _capi.check(_capi.lib().d2p_batch_job_stats(self._h, C.c_void_p(stream), njobs, clipped, peak))
+        return [float(x) for x in peak[:njobs]], [int(x) for x in clipped[:njobs]]
+
+    def stats_reset(self, stream=0):
+        _capi.check(_capi.lib().d2p_batch_stats_reset(self._h, C.c_void_p(stream)))
+
+    def set_control(self, cancel_flag=None, progress=None):
+        """cancel_flag: ctypes.c_int32 the caller may raise at any time; progress(frames_done, frames_total)."""
+        self._cancel = cancel_flag
+        self._progress = _capi.PROGRESS_FN(lambda _u, done, total: progress(done, total)) if progress else _capi.PROGRESS_FN()
+        _capi.check(_capi.lib().d2p_batch_set_control(self._h, C.byref(cancel_flag) if cancel_flag is not None else None,
+                                                      self._progress, None))
+
     def launches(self):
         return int(_capi.lib().d2p_batch_launches(self._h))
 
@@ -283,12 +300,18 @@ def write_flac_file(path, bits, channels, rate, payload, frames, comments=()):
 
 def convert_file(in_path, out_path, out_rate=352800, filt="E", bits=24, dither="X", level_db=0.0, container="W",
                  dither_seed=0, device=0, dsf_stop_at_sample_count=False, raw_channels=2, raw_layout="P",
-                 raw_lsb_first=True, raw_dsd_rate=1, raw_block_size=4096):
-    """One DSF / DSDIFF / raw DSD file -> one PCM file on the GPU (d2p_convert_file).  Returns a dict."""
+                 raw_lsb_first=True, raw_dsd_rate=1, raw_block_size=4096, cancel_flag=None, progress=None):
+    """One DSF / DSDIFF / raw DSD file -> one PCM file on the GPU (d2p_convert_file[_ex]).  Returns a dict.
+    cancel_flag: ctypes.c_int32 that may be raised while the call runs; progress(frames_done, frames_total)."""
     opt = _capi.FileOptions(out_rate, ord(filt), bits, ord(dither), level_db, ord(container), dither_seed, device,
                             1 if dsf_stop_at_sample_count else 0, raw_channels, ord(raw_layout),
                             1 if raw_lsb_first else 0, raw_dsd_rate, raw_block_size)
     res = _capi.FileResult()
-    _capi.check(_capi.lib().d2p_convert_file(C.byref(opt), str(in_path).encode(), str(out_path).encode(), C.byref(res)))
+    if cancel_flag is None and progress is None:
+        _capi.check(_capi.lib().d2p_convert_file(C.byref(opt), str(in_path).encode(), str(out_path).encode(), C.byref(res)))
+    else:
+        cb = _capi.PROGRESS_FN(lambda _u, done, total: progress(done, total)) if progress else _capi.PROGRESS_FN()
+        _capi.check(_capi.lib().d2p_convert_file_ex(C.byref(opt), str(in_path).encode(), str(out_path).encode(), C.byref(res),
+                                                    C.byref(cancel_flag) if cancel_flag is not None else None, cb, None))
     return {"in": _info_dict(res.info), "frames": int(res.frames), "out_bytes": int(res.out_bytes),
-            "clipped_samples": int(res.clipped_samples), "peak_abs": float(res.peak_abs)}
+            "clipped_samples": int(res.clipped_samples), "peak_abs": float(res.peak_abs), "dither_seed": int(res.dither_seed)}

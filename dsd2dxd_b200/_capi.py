@@ -13,7 +13,8 @@ LIB_PATH = os.path.join(_HERE, "libdsd2pcm_b200.so")
 
 OK = 0
 ERR_INVALID_ARG, ERR_TAPS_NOT_FOUND, ERR_UNSUPPORTED_LM, ERR_BIT_DEPTH = 1, 2, 3, 4
-ERR_NO_DEVICE, ERR_CUDA, ERR_NOMEM, ERR_STATE, ERR_CAPACITY = 5, 6, 7, 8, 9
+ERR_NO_DEVICE, ERR_CUDA, ERR_NOMEM, ERR_STATE, ERR_CAPACITY, ERR_CANCELLED = 5, 6, 7, 8, 9, 10
+PROGRESS_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_uint64, C.c_uint64)
 OUT_INTERLEAVED_LE, OUT_INTERLEAVED_BE, OUT_PLANAR_32, OUT_NONE = 0, 1, 2, 3
 
 
@@ -72,7 +73,7 @@ class FileOptions(C.Structure):
 
 class FileResult(C.Structure):
     _fields_ = [("info", ContainerInfo), ("frames", C.c_uint64), ("out_bytes", C.c_uint64),
-                ("clipped_samples", C.c_int64), ("peak_abs", C.c_double)]
+                ("clipped_samples", C.c_int64), ("peak_abs", C.c_double), ("dither_seed", C.c_uint64)]
 
 
 # every symbol include/dsd2pcm_b200.h and include/dsd2pcm_b200_files.h declare
@@ -82,8 +83,8 @@ EXPORTS = [
     "d2p_create", "d2p_destroy", "d2p_push", "d2p_flush", "d2p_set_push_threshold", "d2p_finish", "d2p_frames_ready", "d2p_pull", "d2p_pull_f64", "d2p_stats",
     "d2p_convert_host", "d2p_check_level", "d2p_host_alloc", "d2p_host_free",
     "d2p_batch_create", "d2p_batch_destroy", "d2p_batch_run", "d2p_batch_convert_host", "d2p_batch_launches",
-    "d2p_batch_stats", "d2p_total_frames", "d2p_block_range", "d2p_batch_run_blocks",
-    "d2p_container_parse", "d2p_container_open", "d2p_pcm_header", "d2p_write_pcm_file", "d2p_write_flac_file", "d2p_convert_file",
+    "d2p_batch_stats", "d2p_batch_stats_reset", "d2p_batch_job_stats", "d2p_batch_set_control", "d2p_total_frames", "d2p_block_range", "d2p_batch_run_blocks",
+    "d2p_container_parse", "d2p_container_open", "d2p_pcm_header", "d2p_write_pcm_file", "d2p_write_flac_file", "d2p_convert_file", "d2p_convert_file_ex",
 ]
 
 _lib = None
@@ -136,6 +137,9 @@ def lib():
     L.d2p_batch_launches.restype = C.c_uint64
     L.d2p_batch_launches.argtypes = [vp]
     L.d2p_batch_stats.argtypes = [vp, vp, C.POINTER(C.c_int64), C.POINTER(C.c_double)]
+    L.d2p_batch_stats_reset.argtypes = [vp, vp]
+    L.d2p_batch_job_stats.argtypes = [vp, vp, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_double)]
+    L.d2p_batch_set_control.argtypes = [vp, C.POINTER(C.c_int32), PROGRESS_FN, vp]
     L.d2p_total_frames.restype = C.c_uint64
     L.d2p_total_frames.argtypes = [cfgp, C.c_uint64]
     L.d2p_block_range.argtypes = [cfgp, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
@@ -148,6 +152,8 @@ def lib():
     L.d2p_write_pcm_file.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_uint32, vp, C.c_uint64]
     L.d2p_write_flac_file.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_uint32, vp, C.c_uint64, C.POINTER(C.c_char_p), C.c_int]
     L.d2p_convert_file.argtypes = [C.POINTER(FileOptions), C.c_char_p, C.c_char_p, C.POINTER(FileResult)]
+    L.d2p_convert_file_ex.argtypes = [C.POINTER(FileOptions), C.c_char_p, C.c_char_p, C.POINTER(FileResult),
+                                      C.POINTER(C.c_int32), PROGRESS_FN, vp]
     _lib = L
     return L
 

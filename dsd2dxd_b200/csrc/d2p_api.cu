@@ -197,7 +197,7 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
 
     const size_t budget = (size_t)kMaxSmem - 1024;
     if (dp->lm) {
-        if (p.gmax > 5 || p.ring_cap != 32 || (int)p.L > kMaxPhasesDev)
+        if (p.gmax > 5 || p.ring_cap != 32 || p.lm_reach() > 31 || (int)p.L > kMaxPhasesDev)   // lm_tile_header's window
             return set_err(D2P_ERR_INVALID_ARG, "internal: stage-1 filter outside the kernel's group / ring assumptions");
         const LmLut ll = lm_lut_layout(p);
         const int cons = p.nstages == 3 ? kLmConsumers : kLmConsumersSmall;   // see d2p_launch.h
@@ -402,6 +402,9 @@ struct Launcher {
     uint32_t* d_fpd[kRing] = {nullptr, nullptr, nullptr, nullptr};   // dither F: per-sample xorshift32 states of a launch
     size_t fpd_cap[kRing] = {0, 0, 0, 0};
     uint64_t launches = 0;
+    bool want_jobstats = false;                                      // batch objects: peak / clipped samples per job
+    DevJobStats* d_jobstats = nullptr;
+    int jobstats_cap = 0, jobstats_n = 0;
 
     int init(bool want_events) {
         CK(cudaMalloc(&d_stats, sizeof(DevStats)));
@@ -419,6 +422,7 @@ struct Launcher {
         }
         if (d_stats) cudaFree(d_stats);
         if (d_events) cudaFree(d_events);
+        if (d_jobstats) cudaFree(d_jobstats);
     }
 
     // Dither F needs 4 bytes of xorshift state per output sample of a launch: long jobs are cut into pieces of at
@@ -426,6 +430,15 @@ struct Launcher {
     static const long long kFpdSamples = 256ll << 20;
     int run(const DevicePlan& dp, std::vector<DevJob>& jobs, cudaStream_t stream) {
         for (size_t i = 0; i < jobs.size(); ++i) jobs[i].job_id = (int)i;
+        if (want_jobstats) {                                         // table of the most recent run, indexed by job
+            if (jobstats_cap < (int)jobs.size()) {
+                if (d_jobstats) cudaFree(d_jobstats);
+                jobstats_cap = (int)jobs.size() + 16;
+                CK(cudaMalloc(&d_jobstats, sizeof(DevJobStats) * jobstats_cap));
+            }
+            jobstats_n = (int)jobs.size();
+            if (jobstats_n) CK(cudaMemsetAsync(d_jobstats, 0, sizeof(DevJobStats) * jobstats_n, stream));
+        }
         if (dp.plan.cfg.dither != D2P_DITHER_FPD) return run_once(dp, jobs, stream, false);
         const d2p_config& c = dp.plan.cfg;
         const long long cap_frames = std::max<long long>(kFpdSamples / c.channels, dp.kp.TF);
@@ -508,6 +521,7 @@ struct Launcher {
         k.njobs = (int)live.size();
         k.total_tiles = (unsigned int)tiles;
         k.stats = d_stats;
+        k.job_stats = want_jobstats ? d_jobstats : nullptr;
         k.events = d_events;
         k.ev_cap = d_events ? kEventCap : 0;
         const unsigned long long want = (unsigned long long)dp.num_sms * dp.ctas_per_sm;
@@ -711,6 +725,7 @@ const char* d2p_strerror(int status) {
     case D2P_ERR_NOMEM: return "out of memory";
     case D2P_ERR_STATE: return "invalid call sequence";
     case D2P_ERR_CAPACITY: return "output buffer too small";
+    case D2P_ERR_CANCELLED: return "conversion cancelled";
     default: return "unknown status";
     }
 }
@@ -991,11 +1006,13 @@ struct HostPipe {
     uint8_t* d_in[NS] = {nullptr, nullptr, nullptr};
     uint8_t* d_out[NS] = {nullptr, nullptr, nullptr};
     size_t in_cap = 0, out_cap = 0;
+    cudaEvent_t done[NS] = {nullptr, nullptr, nullptr};            // chunk on stream s has landed in the caller's buffer
     bool ready = false;
 
     int init() {
         if (ready) return D2P_OK;
         for (int s = 0; s < NS; ++s) CK(cudaStreamCreateWithFlags(&streams[s], cudaStreamNonBlocking));
+        for (int s = 0; s < NS; ++s) CK(cudaEventCreateWithFlags(&done[s], cudaEventDisableTiming));
         ready = true;
         return D2P_OK;
     }
@@ -1015,14 +1032,25 @@ struct HostPipe {
     void destroy() {
         for (int s = 0; s < NS; ++s) {
             if (streams[s]) { cudaStreamSynchronize(streams[s]); cudaStreamDestroy(streams[s]); }
+            if (done[s]) cudaEventDestroy(done[s]);
             if (d_in[s]) cudaFree(d_in[s]);
             if (d_out[s]) cudaFree(d_out[s]);
         }
     }
 };
 
+// Cancellation and progress: the reference polls its cancel flag once per reader block and reports
+// progress through track_io (rd/conversion_context.rs:222, 304-308, 331-371).  Here both are honoured between pipeline
+// chunks: the host thread never runs more than NS chunks ahead of the device, so frames_done is what has really
+// arrived in the caller's buffer and a raised flag stops the call within a few chunks.
+struct HostControl {
+    const volatile int32_t* cancel = nullptr;
+    d2p_progress_fn progress = nullptr;
+    void* user = nullptr;
+};
+
 static int host_convert(const DevicePlan& dp, Launcher& launcher, HostPipe& pipe, const uint8_t* raw, size_t nbytes,
-                        void* pcm, size_t out_cap_bytes, uint64_t* frames, size_t chunk_bytes) {
+                        void* pcm, size_t out_cap_bytes, uint64_t* frames, size_t chunk_bytes, const HostControl& ctl = HostControl()) {
     const Plan& p = dp.plan;
     const d2p_config& c = p.cfg;
     const bool planar = c.in_layout == D2P_LAYOUT_PLANAR;
@@ -1049,7 +1077,16 @@ static int host_convert(const DevicePlan& dp, Launcher& launcher, HostPipe& pipe
 
     long long f_done = 0;
     int ci = 0;
+    long long f_upto[HostPipe::NS] = {0, 0, 0};                       // frames complete once stream s has drained
+    const bool controlled = ctl.cancel || ctl.progress;
     for (long long g0 = 0;;) {
+        if (controlled && ci >= HostPipe::NS) {                       // chunk ci - NS shares this chunk's staging buffers
+            const int s = ci % HostPipe::NS;
+            cudaError_t e = cudaEventSynchronize(pipe.done[s]);
+            if (e != cudaSuccess) { rc = cuda_err(e, "chunk sync"); break; }
+            if (ctl.progress) ctl.progress(ctl.user, (uint64_t)f_upto[s], (uint64_t)total_frames);
+        }
+        if (ctl.cancel && *ctl.cancel) { rc = set_err(D2P_ERR_CANCELLED, "conversion cancelled"); break; }
         const long long g1 = std::min(groups, g0 + chunk_groups);
         const bool last = g1 >= groups;
         const long long end_q = g1 * unit + (last ? tail_per : 0);
@@ -1077,6 +1114,11 @@ static int host_convert(const DevicePlan& dp, Launcher& launcher, HostPipe& pipe
                 if (e != cudaSuccess) { rc = cuda_err(e, "D2H"); break; }
             }
             f_done = f_new;
+            if (controlled) {
+                f_upto[s] = f_done;
+                e = cudaEventRecord(pipe.done[s], pipe.streams[s]);
+                if (e != cudaSuccess) { rc = cuda_err(e, "event record"); break; }
+            }
         }
         if (last) break;
         g0 = g1;
@@ -1085,7 +1127,10 @@ static int host_convert(const DevicePlan& dp, Launcher& launcher, HostPipe& pipe
         cudaError_t e = cudaStreamSynchronize(pipe.streams[s]);
         if (e != cudaSuccess && rc == D2P_OK) rc = cuda_err(e, "stream sync");
     }
-    if (rc == D2P_OK) *frames = (uint64_t)f_done;
+    if (rc == D2P_OK) {
+        *frames = (uint64_t)f_done;
+        if (ctl.progress) ctl.progress(ctl.user, (uint64_t)f_done, (uint64_t)total_frames);
+    }
     return rc;
 }
 }  // namespace d2p
@@ -1095,6 +1140,7 @@ struct d2p_batch {
     DevicePlan* dp = nullptr;
     Launcher launcher;
     HostPipe pipe;
+    HostControl ctl;
 };
 
 int d2p_batch_create(const d2p_config* cfg, d2p_batch** out) {
@@ -1105,6 +1151,7 @@ int d2p_batch_create(const d2p_config* cfg, d2p_batch** out) {
     if (st != D2P_OK) return st;
     d2p_batch* b = new d2p_batch();
     b->dp = dp;
+    b->launcher.want_jobstats = true;
     st = b->launcher.init(false);
     if (st != D2P_OK) { d2p_batch_destroy(b); return st; }
     *out = b;
@@ -1134,7 +1181,13 @@ int d2p_batch_convert_host(d2p_batch* b, const uint8_t* raw, size_t nbytes, void
         const long mb = e ? std::atol(e) : 0;
         return (size_t)(mb >= 1 && mb <= 1024 ? mb : 64) << 20;
     }();
-    return host_convert(*b->dp, b->launcher, b->pipe, raw, nbytes, pcm, out_cap_bytes, frames, chunk);
+    return host_convert(*b->dp, b->launcher, b->pipe, raw, nbytes, pcm, out_cap_bytes, frames, chunk, b->ctl);
+}
+
+int d2p_batch_set_control(d2p_batch* b, const volatile int32_t* cancel_flag, d2p_progress_fn progress, void* user) {
+    if (!b) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    b->ctl.cancel = cancel_flag; b->ctl.progress = progress; b->ctl.user = user;
+    return D2P_OK;
 }
 
 int d2p_convert_host(const d2p_config* cfg, const uint8_t* raw, size_t nbytes, void* pcm, size_t out_cap_bytes,
@@ -1261,6 +1314,27 @@ int d2p_batch_run_blocks(d2p_batch* b, const d2p_block_job* jobs, int njobs, voi
 }
 
 uint64_t d2p_batch_launches(const d2p_batch* b) { return b ? b->launcher.launches : 0; }
+
+int d2p_batch_job_stats(d2p_batch* b, void* cuda_stream, int njobs, int64_t* clipped_samples, double* peak_abs) {
+    if (!b || njobs < 0) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    if (njobs > b->launcher.jobstats_n) return set_err(D2P_ERR_INVALID_ARG, "more jobs asked for than the last run had");
+    CK(cudaSetDevice(b->dp->plan.cfg.device));
+    std::vector<DevJobStats> st((size_t)njobs);
+    if (njobs) CK(cudaMemcpyAsync(st.data(), b->launcher.d_jobstats, sizeof(DevJobStats) * njobs, cudaMemcpyDeviceToHost, (cudaStream_t)cuda_stream));
+    CK(cudaStreamSynchronize((cudaStream_t)cuda_stream));
+    for (int i = 0; i < njobs; ++i) {
+        if (clipped_samples) clipped_samples[i] = (int64_t)st[i].clipped;
+        if (peak_abs) std::memcpy(&peak_abs[i], &st[i].peak_bits, 8);
+    }
+    return D2P_OK;
+}
+
+int d2p_batch_stats_reset(d2p_batch* b, void* cuda_stream) {
+    if (!b) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    CK(cudaSetDevice(b->dp->plan.cfg.device));
+    CK(cudaMemsetAsync(b->launcher.d_stats, 0, sizeof(DevStats), (cudaStream_t)cuda_stream));
+    return D2P_OK;
+}
 
 int d2p_batch_stats(d2p_batch* b, void* cuda_stream, int64_t* clipped_samples, double* peak_abs) {
     if (!b) return set_err(D2P_ERR_INVALID_ARG, "null argument");

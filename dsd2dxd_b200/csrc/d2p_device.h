@@ -40,6 +40,8 @@ struct DevStats {
     unsigned int pad;
 };
 
+struct DevJobStats { unsigned long long peak_bits, clipped; };   // per job_id (device-resident batches)
+
 struct ClipEvent { int job; int ch_kind; long long frame; };   // ch_kind = channel | (1<<16 if high clip)
 
 static const int kMaxPhasesDev = 20;
@@ -100,6 +102,7 @@ struct KParams {
     unsigned int fpd_items;
 
     DevStats* stats;
+    DevJobStats* job_stats;   // optional table indexed by DevJob::job_id
     ClipEvent* events;
     unsigned int ev_cap;
 

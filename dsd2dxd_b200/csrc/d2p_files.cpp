@@ -12,6 +12,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <random>
 #include <string>
 #include <vector>
 
@@ -43,7 +44,8 @@ int parse_dsf(const uint8_t* b, size_t n, uint64_t file_bytes, d2p_container_inf
     const uint8_t* f = b + 28;
     if (!tag(f, "fmt ")) return api_set_error(D2P_ERR_INVALID_ARG, "DSF: fmt chunk missing");
     const uint64_t fmt_size = le64(f + 4);
-    if (fmt_size < 52 || 28 + fmt_size + 12 > n) return api_set_error(D2P_ERR_INVALID_ARG, "DSF: bad fmt chunk size");
+    if (fmt_size < 52 || fmt_size > n - 40) return        // n >= 92; no sum of file-supplied sizes can wrap
+        api_set_error(D2P_ERR_INVALID_ARG, "DSF: bad fmt chunk size");
     if (le32(f + 12) != 1) return api_set_error(D2P_ERR_INVALID_ARG, "DSF: format version is not 1");
     if (le32(f + 16) != 0) return api_set_error(D2P_ERR_INVALID_ARG, "DSF: format id is not DSD raw");
     o->format = D2P_CONTAINER_DSF;
@@ -101,7 +103,7 @@ int parse_dff(ReadFn read, uint64_t file_bytes, d2p_container_info* o) {
                 while (q + 12 <= p.size()) {
                     const uint64_t s2 = be64(p.data() + q + 4);
                     const uint8_t* d2 = p.data() + q + 12;
-                    if (q + 12 + s2 > p.size()) break;
+                    if (s2 > p.size() - q - 12) break;               // compare without adding: s2 comes from the file
                     if (tag(p.data() + q, "FS  ") && s2 >= 4) o->sample_rate = be32(d2);
                     else if (tag(p.data() + q, "CHNL") && s2 >= 2) o->channels = be16(d2);
                     else if (tag(p.data() + q, "CMPR") && s2 >= 4) dsd_cmpr = tag(d2, "DSD ");
@@ -283,7 +285,24 @@ int d2p_write_pcm_file(const char* path, int container, int bits, int channels, 
     return D2P_OK;
 }
 
+// The reference seeds its dither from the OS for every run (rand::thread_rng, rd/dither.rs:64-76).  A caller that
+// leaves dither_seed at 0 gets the same behaviour: a seed drawn from the OS entropy source mixed with a hash of the
+// input path, so that no two files share a noise sequence.  A non-zero seed is used as given (reproducible runs).
+static uint64_t file_dither_seed(uint64_t given, int dither, const char* path) {
+    if (given != 0 || dither == D2P_DITHER_NONE) return given;
+    uint64_t h = 0xcbf29ce484222325ull;                           // FNV-1a of the path
+    for (const char* c = path; *c; ++c) { h ^= (uint8_t)*c; h *= 0x100000001b3ull; }
+    std::random_device rd;
+    h ^= ((uint64_t)rd() << 32) | rd();
+    return h ? h : 1;
+}
+
 int d2p_convert_file(const d2p_file_options* opt, const char* in_path, const char* out_path, d2p_file_result* res) {
+    return d2p_convert_file_ex(opt, in_path, out_path, res, nullptr, nullptr, nullptr);
+}
+
+int d2p_convert_file_ex(const d2p_file_options* opt, const char* in_path, const char* out_path, d2p_file_result* res,
+                        const volatile int32_t* cancel_flag, d2p_progress_fn progress, void* user) {
     if (!opt || !in_path || !out_path) return api_set_error(D2P_ERR_INVALID_ARG, "null argument");
     d2p_file_result local;
     d2p_file_result& R = res ? *res : local;
@@ -323,7 +342,8 @@ int d2p_convert_file(const d2p_file_options* opt, const char* in_path, const cha
     cfg.block_size = ci.in_layout == D2P_LAYOUT_INTERLEAVED ? 4096u : ci.block_size;   // interleaved: reader chunk only
     cfg.out_format = (opt->out_container == D2P_FILE_AIFF || opt->out_container == D2P_FILE_AIFC) ? D2P_OUT_INTERLEAVED_BE
                                                                                                   : D2P_OUT_INTERLEAVED_LE;
-    cfg.dither_seed = opt->dither_seed; cfg.device = opt->device;
+    cfg.dither_seed = file_dither_seed(opt->dither_seed, opt->dither, in_path); cfg.device = opt->device;
+    R.dither_seed = cfg.dither_seed;
     d2p_plan_info pi;
     int st = d2p_plan(&cfg, &pi);
     if (st != D2P_OK) return st;
@@ -352,11 +372,22 @@ int d2p_convert_file(const d2p_file_options* opt, const char* in_path, const cha
         in_bytes = (size_t)(full * group + tail * ci.channels);
     }
     uint64_t frames = 0;
-    st = d2p_convert_host(&cfg, h_in, in_bytes, h_out, out_cap, &frames, &R.clipped_samples, &R.peak_abs);
-    if (st != D2P_OK) return st;
+    {
+        d2p_batch* b = nullptr;
+        st = d2p_batch_create(&cfg, &b);
+        if (st != D2P_OK) return st;
+        d2p_batch_set_control(b, cancel_flag, progress, user);
+        st = d2p_batch_convert_host(b, h_in, in_bytes, h_out, out_cap, &frames);
+        if (st == D2P_OK) st = d2p_batch_stats(b, nullptr, &R.clipped_samples, &R.peak_abs);
+        d2p_batch_destroy(b);
+        if (st != D2P_OK) return st;                               // nothing has been written yet
+    }
     R.frames = frames;
     st = d2p_write_pcm_file(out_path, opt->out_container, opt->bits, ci.channels, opt->out_rate, h_out, frames);
-    if (st != D2P_OK) return st;
+    if (st != D2P_OK) {                                            // no partly written file is left behind
+        if (std::strncmp(out_path, "/dev/", 5) != 0) std::remove(out_path);
+        return st;
+    }
     if (opt->out_container == D2P_FILE_FLAC) {                     // compressed: the size is whatever the encoder produced
         FileCloser of{std::fopen(out_path, "rb")};
         if (of.f && std::fseek(of.f, 0, SEEK_END) == 0) R.out_bytes = (uint64_t)std::ftell(of.f);

@@ -287,9 +287,15 @@ struct Emitter {
     unsigned long long peakb;          // max |sample*scale| as f64 bits (non-negative doubles order as integers)
     unsigned int clip_lo, clip_hi;
     uint32_t key;
+    int job;                           // job whose statistics are being accumulated (per-job table only)
 
-    __device__ __forceinline__ void init() { peakb = 0ull; clip_lo = 0; clip_hi = 0; key = 0; }
-    __device__ __forceinline__ void set_job(const DevJob& J) { key = philox_key(J.seed); }
+    __device__ __forceinline__ void init() { peakb = 0ull; clip_lo = 0; clip_hi = 0; key = 0; job = -1; }
+    // called by every consumer thread of the CTA for every tile (warp-uniform): with a per-job table the
+    // accumulators are handed over whenever the tile belongs to another job (dsd_levels: one peak per file)
+    __device__ __forceinline__ void set_job(const KParams& P, const DevJob& J) {
+        if (P.job_stats && J.job_id != job) { if (job >= 0) flush(P); job = J.job_id; }
+        key = philox_key(J.seed);
+    }
 
     __device__ __forceinline__ void clip_event(const KParams& P, const DevJob& J, int ch, long long f, int high) {
         if (high) ++clip_hi; else ++clip_lo;
@@ -394,7 +400,12 @@ struct Emitter {
             if (pb) atomicMax(&P.stats->peak_bits, pb);
             if (clip_lo) atomicAdd(&P.stats->clip_lo, (unsigned long long)clip_lo);
             if (clip_hi) atomicAdd(&P.stats->clip_hi, (unsigned long long)clip_hi);
+            if (P.job_stats && job >= 0) {
+                if (pb) atomicMax(&P.job_stats[job].peak_bits, pb);
+                if (clip_lo | clip_hi) atomicAdd(&P.job_stats[job].clipped, (unsigned long long)clip_lo + clip_hi);
+            }
         }
+        peakb = 0ull; clip_lo = 0; clip_hi = 0;
     }
 };
 
@@ -703,7 +714,7 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
             const unsigned char* tiles = inbuf + (size_t)bsel * P.in_buf_bytes;
             unsigned char* ostage = obuf + (size_t)bsel * P.ostage_bytes;
             const int bpo = P.bpo;
-            em.set_job(*t.J);
+            em.set_job(P, *t.J);
             // One item = one frame set: slot s of channel ch holds the frames fl0 + f*fpw, f < F, with
             // fl0 = (s / fpw) * F * fpw + s % fpw  (fpw = frames per 32-bit word of the stream, 1 unless bpo < 4).
             const int items = P.C << P.sl_shift;
@@ -921,7 +932,7 @@ __global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __gri
             const DevJob& J = *H.J;
             const unsigned char* tiles = tiles0 + (size_t)bsel * tiles_bytes;
             unsigned char* ostage = ostage0 + (size_t)bsel * P.ostage_bytes;
-            em.set_job(J);
+            em.set_job(P, J);
             const long long f0 = H.f0;
             const int nf = H.nf, cnt2 = H.cnt2, last_rel = H.last_rel, relz = H.relz;
 

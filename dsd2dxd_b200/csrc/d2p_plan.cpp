@@ -1,6 +1,7 @@
 // d2p_plan.cpp -- see d2p_plan.h.  Host only; compiled with FP contraction off.
 #include "d2p_plan.h"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -112,6 +113,14 @@ long long Plan::bytes_needed_for_frames(long long nframes) const {
     return hi;
 }
 
+// Oldest input bit, counted back from the newest one, that a stage-1 output reads: group g looks at the 8-bit window
+// ending 8g bits back, taken modulo the reference's byte ring (Stage1Poly, rd/lm_resampler.rs:408-450, 603-640).
+int Plan::lm_reach() const {
+    int reach = 7;
+    for (int g = 0; g < gmax; ++g) reach = std::max(reach, (8 * g) % ring_cap + 7);
+    return reach;
+}
+
 long long Plan::first_byte_needed(long long f) const {
     long long q;
     if (nstages == 1) {
@@ -122,7 +131,7 @@ long long Plan::first_byte_needed(long long f) const {
         long long n = (h2 - 1) + k2 * D2 - (2LL * h2 - 1);
         if (n < 0) n = 0;
         const long long t = stage1_nhi(n) / (long long)L;
-        q = (t - 31) >> 3;
+        q = (t - std::max(lm_reach(), 31)) >> 3;                // the kernels always stage a 32-bit window per output
     }
     return q > 0 ? q : 0;
 }
@@ -137,6 +146,7 @@ int make_plan(const d2p_config& cfg, Plan* out, std::string* msg) {
     if (cfg.in_layout != D2P_LAYOUT_PLANAR && cfg.in_layout != D2P_LAYOUT_INTERLEAVED)
         return fail(D2P_ERR_INVALID_ARG, "Invalid format; must be I (interleaved) or P (planar)");
     if (cfg.block_size == 0) return fail(D2P_ERR_INVALID_ARG, "block_size must be > 0");
+    if (cfg.block_size > 0x7FFFFFFFu) return fail(D2P_ERR_INVALID_ARG, "block_size must be below 2^31");
     if (!(cfg.dither == 'T' || cfg.dither == 'R' || cfg.dither == 'F' || cfg.dither == 'X'))
         return fail(D2P_ERR_INVALID_ARG, "Invalid dither type; must be T, R, F, or X");
     if (cfg.out_format < 0 || cfg.out_format > 3) return fail(D2P_ERR_INVALID_ARG, "invalid out_format");
@@ -187,6 +197,15 @@ int make_plan(const d2p_config& cfg, Plan* out, std::string* msg) {
         }
         p.tab[0] = t; p.sdecim[0] = p.M; p.nstages = 1;
         p.h = t->len; p.nt = (p.h + 7) / 8; p.bpo = p.M / 8;
+        // process_bytes restarts its byte-in-frame counter on every call (rd/byte_precalc_decimator.rs:121-123): with a
+        // block that is not a whole number of output frames the reference drops the partial frame of every block and
+        // its frame phase drifts.  The closed forms here assume continuous frames, so such a block size is refused
+        // rather than converted differently (4096 and every power of two >= 16 are fine).
+        if (cfg.block_size % (uint32_t)p.bpo != 0) {
+            char buf[160];
+            std::snprintf(buf, sizeof buf, "block_size %u is not a multiple of the %d input bytes per output frame", cfg.block_size, p.bpo);
+            return fail(D2P_ERR_INVALID_ARG, buf);
+        }
     }
 
     // set_scaling  rd/pcm_writer.rs:288-298

@@ -62,6 +62,8 @@ struct Plan {
     long long frames_for_bytes(long long bytes) const;
     // smallest per-channel byte count whose frames_for_bytes() is >= nframes
     long long bytes_needed_for_frames(long long nframes) const;
+    // L/M: how many bits behind its newest input bit a stage-1 output reads (31 for every table in use)
+    int lm_reach() const;
     // oldest per-channel byte position (>= 0) that the computation of frame f reads
     long long first_byte_needed(long long f) const;
 };

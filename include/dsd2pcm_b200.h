@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define D2P_ABI_VERSION 1
+#define D2P_ABI_VERSION 2
 
 typedef enum d2p_status {
     D2P_OK = 0,
@@ -39,7 +39,8 @@ typedef enum d2p_status {
     D2P_ERR_CUDA = 6,             /* a CUDA call failed; d2p_last_error() has the detail */
     D2P_ERR_NOMEM = 7,
     D2P_ERR_STATE = 8,            /* call sequence error (push after finish, ...) */
-    D2P_ERR_CAPACITY = 9          /* output buffer too small */
+    D2P_ERR_CAPACITY = 9,         /* output buffer too small */
+    D2P_ERR_CANCELLED = 10        /* the caller's cancel flag was raised (cancel_flag, rd/conversion_context.rs:222, 304-308) */
 } d2p_status;
 
 /* Values are the reference CLI's own option letters (src/main.rs:171-215). */
@@ -175,10 +176,21 @@ int  d2p_batch_run(d2p_batch* b, d2p_job* jobs, int njobs, void* cuda_stream);
  * d2p_convert_host() is this call on a temporary batch object. */
 int  d2p_batch_convert_host(d2p_batch* b, const uint8_t* raw, size_t nbytes, void* pcm, size_t out_cap_bytes,
                             uint64_t* frames);
+/* Cancellation and progress of d2p_batch_convert_host (and of what is built on it: d2p_convert_file_ex).
+ * The reference polls `cancel_flag: &AtomicBool` once per reader block and reports through track_io
+ * (rd/conversion_context.rs:222, 304-308, 331-371; rd/lib.rs:275-281 do_conversion).  Here *cancel_flag is read and
+ * `progress` is called between pipeline chunks (64 MiB of input), from the calling thread; frames_done counts frames
+ * that have arrived in the caller's buffer.  A raised flag ends the call with D2P_ERR_CANCELLED.  NULLs switch it off. */
+typedef void (*d2p_progress_fn)(void* user, uint64_t frames_done, uint64_t frames_total);
+int  d2p_batch_set_control(d2p_batch* b, const volatile int32_t* cancel_flag, d2p_progress_fn progress, void* user);
 /* Number of kernel launches issued by this batch object so far. */
 uint64_t d2p_batch_launches(const d2p_batch* b);
-/* Sum over jobs of clipped samples / max |sample*scale| since creation (synchronises the stream). */
+/* Sum over jobs of clipped samples / max |sample*scale| since creation or the last reset (synchronises the stream). */
 int  d2p_batch_stats(d2p_batch* b, void* cuda_stream, int64_t* clipped_samples, double* peak_abs);
+int  d2p_batch_stats_reset(d2p_batch* b, void* cuda_stream);
+/* Per job of the most recent d2p_batch_run / d2p_batch_run_blocks (dsd_levels reports one peak per file,
+ * src/bin/dsd_levels/main.rs:207): arrays of njobs entries, either may be NULL.  Synchronises the stream. */
+int  d2p_batch_job_stats(d2p_batch* b, void* cuda_stream, int njobs, int64_t* clipped_samples, double* peak_abs);
 
 /* ---- time-block split of one long payload -------------------------------------------- */
 /* Every output frame is a pure function of a bounded input window, so a payload can be cut in

@@ -80,7 +80,8 @@ typedef struct d2p_file_options {
     int32_t  dither;          /* -d  D2P_DITHER_* */
     double   level_db;        /* -l */
     int32_t  out_container;   /* -o  D2P_FILE_* */
-    uint64_t dither_seed;
+    uint64_t dither_seed;     /* 0 with a dither other than X: drawn from the OS per file, like the reference's thread_rng
+                                 (rd/dither.rs:64-76); the value used is reported in d2p_file_result.dither_seed */
     int32_t  device;
     int32_t  dsf_stop_at_sample_count;   /* 0: convert every whole block of the data chunk; 1: stop at fmt.sample_count */
     /* raw input (.dsd / anything that is not DSF or DSDIFF): the CLI's -c -f -e -s -i */
@@ -94,11 +95,17 @@ typedef struct d2p_file_result {
     uint64_t out_bytes;       /* size of the file written */
     int64_t  clipped_samples;
     double   peak_abs;
+    uint64_t dither_seed;     /* the seed the conversion used (see d2p_file_options.dither_seed) */
 } d2p_file_result;
 
 /* One input file -> one PCM file: parse the container, stream the payload through the GPU
  * (d2p_convert_host: pinned staging, H2D / kernel / D2H overlapped), write header + payload. */
 int d2p_convert_file(const d2p_file_options* opt, const char* in_path, const char* out_path, d2p_file_result* res);
+/* The same with the reference's cancellation flag and progress report (Rdsd2Pcm::do_conversion(&AtomicBool,
+ * Option<Sender<ProgressUpdate>>), rd/lib.rs:275-281): see d2p_batch_set_control.  A cancelled or failed conversion
+ * leaves no output file behind. */
+int d2p_convert_file_ex(const d2p_file_options* opt, const char* in_path, const char* out_path, d2p_file_result* res,
+                        const volatile int32_t* cancel_flag, d2p_progress_fn progress, void* user);
 
 #ifdef __cplusplus
 }

@@ -5,7 +5,7 @@
 #![allow(non_camel_case_types)]
 use std::os::raw::{c_char, c_int, c_void};
 
-pub const D2P_ABI_VERSION: c_int = 1;
+pub const D2P_ABI_VERSION: c_int = 2;
 
 // d2p_status
 pub const D2P_OK: c_int = 0;
@@ -18,6 +18,7 @@ pub const D2P_ERR_CUDA: c_int = 6;
 pub const D2P_ERR_NOMEM: c_int = 7;
 pub const D2P_ERR_STATE: c_int = 8;
 pub const D2P_ERR_CAPACITY: c_int = 9;
+pub const D2P_ERR_CANCELLED: c_int = 10;
 
 // FilterType (rd/lib.rs:313-323), DitherType (rd/lib.rs:301-311), FmtType
 pub const D2P_FILTER_EQUIRIPPLE: i32 = b'E' as i32;
@@ -162,7 +163,11 @@ pub struct d2p_file_result {
     pub out_bytes: u64,
     pub clipped_samples: i64,
     pub peak_abs: f64,
+    pub dither_seed: u64,
 }
+
+/// `progress` of d2p_batch_set_control / d2p_convert_file_ex: (user, frames_done, frames_total)
+pub type d2p_progress_fn = Option<unsafe extern "C" fn(user: *mut c_void, frames_done: u64, frames_total: u64)>;
 
 extern "C" {
     pub fn d2p_abi_version() -> c_int;
@@ -207,6 +212,12 @@ extern "C" {
                                   frames: *mut u64) -> c_int;
     pub fn d2p_batch_launches(b: *const d2p_batch) -> u64;
     pub fn d2p_batch_stats(b: *mut d2p_batch, cuda_stream: *mut c_void, clipped_samples: *mut i64, peak_abs: *mut f64) -> c_int;
+    pub fn d2p_batch_stats_reset(b: *mut d2p_batch, cuda_stream: *mut c_void) -> c_int;
+    // one peak per file, as dsd_levels prints it (src/bin/dsd_levels/main.rs:207)
+    pub fn d2p_batch_job_stats(b: *mut d2p_batch, cuda_stream: *mut c_void, njobs: c_int, clipped_samples: *mut i64,
+                               peak_abs: *mut f64) -> c_int;
+    // cancel_flag: &AtomicBool (as *const i32) and the progress channel of do_conversion   rd/lib.rs:275-281
+    pub fn d2p_batch_set_control(b: *mut d2p_batch, cancel_flag: *const i32, progress: d2p_progress_fn, user: *mut c_void) -> c_int;
     pub fn d2p_block_range(cfg: *const d2p_config, payload_bytes: u64, first_frame: u64, frame_count: u64,
                            in_offset: *mut u64, in_bytes: *mut u64) -> c_int;
     pub fn d2p_batch_run_blocks(b: *mut d2p_batch, jobs: *const d2p_block_job, njobs: c_int, cuda_stream: *mut c_void) -> c_int;
@@ -224,4 +235,7 @@ extern "C" {
     // Rdsd2Pcm::from_container + do_conversion + PcmWriter::save_file   rd/lib.rs:171-182, 275-281, rd/pcm_writer.rs:300-318
     pub fn d2p_convert_file(opt: *const d2p_file_options, in_path: *const c_char, out_path: *const c_char,
                             res: *mut d2p_file_result) -> c_int;
+    pub fn d2p_convert_file_ex(opt: *const d2p_file_options, in_path: *const c_char, out_path: *const c_char,
+                               res: *mut d2p_file_result, cancel_flag: *const i32, progress: d2p_progress_fn,
+                               user: *mut c_void) -> c_int;
 }

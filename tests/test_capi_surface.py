@@ -31,7 +31,7 @@ def test_every_declared_symbol_is_exported():
 
 def test_abi_version_and_error_strings():
     L = _capi.lib()
-    assert L.d2p_abi_version() == 1
+    assert L.d2p_abi_version() == 2
     assert b"Taps not found" in L.d2p_strerror(2)
     assert b"Unsupported L/M" in L.d2p_strerror(3)
     assert b"Unsupported bit depth" in L.d2p_strerror(4)
