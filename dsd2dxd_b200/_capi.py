@@ -83,7 +83,7 @@ EXPORTS = [
     "d2p_create", "d2p_destroy", "d2p_push", "d2p_flush", "d2p_set_push_threshold", "d2p_finish", "d2p_frames_ready", "d2p_pull", "d2p_pull_f64", "d2p_stats",
     "d2p_convert_host", "d2p_check_level", "d2p_host_alloc", "d2p_host_free",
     "d2p_batch_create", "d2p_batch_destroy", "d2p_batch_run", "d2p_batch_convert_host", "d2p_batch_launches",
-    "d2p_batch_stats", "d2p_batch_stats_reset", "d2p_batch_job_stats", "d2p_batch_set_control", "d2p_total_frames", "d2p_block_range", "d2p_batch_run_blocks",
+    "d2p_batch_stats", "d2p_batch_stats_reset", "d2p_batch_job_stats", "d2p_batch_set_control", "d2p_total_frames", "d2p_block_range", "d2p_batch_run_blocks", "d2p_debug_fpd_exponent",
     "d2p_container_parse", "d2p_container_open", "d2p_pcm_header", "d2p_write_pcm_file", "d2p_write_flac_file", "d2p_convert_file", "d2p_convert_file_ex",
 ]
 
@@ -138,6 +138,7 @@ def lib():
     L.d2p_batch_launches.argtypes = [vp]
     L.d2p_batch_stats.argtypes = [vp, vp, C.POINTER(C.c_int64), C.POINTER(C.c_double)]
     L.d2p_batch_stats_reset.argtypes = [vp, vp]
+    L.d2p_debug_fpd_exponent.argtypes = [C.POINTER(C.c_double), C.c_int, C.POINTER(C.c_int32), C.c_int]
     L.d2p_batch_job_stats.argtypes = [vp, vp, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_double)]
     L.d2p_batch_set_control.argtypes = [vp, C.POINTER(C.c_int32), PROGRESS_FN, vp]
     L.d2p_total_frames.restype = C.c_uint64

@@ -1315,6 +1315,20 @@ int d2p_batch_run_blocks(d2p_batch* b, const d2p_block_job* jobs, int njobs, voi
 
 uint64_t d2p_batch_launches(const d2p_batch* b) { return b ? b->launcher.launches : 0; }
 
+int d2p_debug_fpd_exponent(const double* samples, int n, int32_t* exponents, int device) {
+    if ((!samples || !exponents) && n > 0) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    if (n <= 0) return D2P_OK;
+    CK(cudaSetDevice(device));
+    double* d_s = nullptr; int* d_e = nullptr;
+    CK(cudaMalloc(&d_s, sizeof(double) * n));
+    if (cudaMalloc(&d_e, sizeof(int) * n) != cudaSuccess) { cudaFree(d_s); return cuda_err(cudaGetLastError(), "cudaMalloc"); }
+    cudaError_t e = cudaMemcpy(d_s, samples, sizeof(double) * n, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = launch_fpd_exponent(d_s, n, d_e, nullptr);
+    if (e == cudaSuccess) e = cudaMemcpy(exponents, d_e, sizeof(int) * n, cudaMemcpyDeviceToHost);
+    cudaFree(d_s); cudaFree(d_e);
+    return e == cudaSuccess ? D2P_OK : cuda_err(e, "fpd exponent");
+}
+
 int d2p_batch_job_stats(d2p_batch* b, void* cuda_stream, int njobs, int64_t* clipped_samples, double* peak_abs) {
     if (!b || njobs < 0) return set_err(D2P_ERR_INVALID_ARG, "null argument");
     if (njobs > b->launcher.jobstats_n) return set_err(D2P_ERR_INVALID_ARG, "more jobs asked for than the last run had");

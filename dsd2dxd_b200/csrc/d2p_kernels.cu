@@ -98,6 +98,35 @@ __device__ __forceinline__ double dither_noise(int kind, unsigned long long fram
     return __dsub_rn(__dmul_rn((double)u, 1.0 / 9007199254740992.0), 0.5);
 }
 
+// Dither::fpdither's octave (rd/dither.rs:102-104): `s.abs().log2().floor() as i32` -- NaN -> 0, saturating.
+// Evaluated WITHOUT a device log2: libdevice's log2 is not exact at powers of two (log2(2^-59) comes out just below
+// -59) and within an ulp everywhere else, so the floor lands in the wrong octave on and next to every octave edge.
+// The reference's value is floor(RN(log2 |s|)) with the host libm's (correctly rounded near the edges) log2:
+//   |s| = m * 2^k, 1 <= m < 2  ->  k, except that for |s| only j doubles below 2^(k+1) the logarithm
+//   (k+1) - j * 2^-53 / ln 2 rounds UP to k+1 when it is closer to k+1 than to the double in front of it, i.e. when
+//   j <= floor(2^q * ln 2) with 2^(q-52) the spacing of the doubles on that side of k+1.
+__device__ __forceinline__ int fpd_exponent(double s) {
+    const unsigned long long b = (unsigned long long)__double_as_longlong(s) & 0x7FFFFFFFFFFFFFFFull;
+    if (b > 0x7FF0000000000000ull) return 0;                       // NaN as i32
+    if (b == 0x7FF0000000000000ull) return INT_MAX;                // log2(inf) = inf, saturates
+    if (b == 0ull) return INT_MIN;                                 // log2(0) = -inf, saturates
+    const int ex = (int)(b >> 52);
+    unsigned long long man = b & 0xFFFFFFFFFFFFFull;
+    int k;
+    if (ex == 0) { const int lz = __clzll((long long)man) - 11; man = (man << lz) & 0xFFFFFFFFFFFFFull; k = -1022 - lz; }
+    else k = ex - 1023;
+    const unsigned long long j = 0x10000000000000ull - man;        // mantissa steps up to the next power of two
+    const int n = k + 1;
+    if (n == 0 || j > 709ull) return k;
+    const unsigned int an = n < 0 ? (unsigned int)(-n) : (unsigned int)n;
+    int q = 31 - __clz((int)an);
+    if (n > 0 && (an & (an - 1)) == 0) --q;                        // below a positive power of two the doubles are twice as dense
+    if (q < 0) return k;
+    const unsigned int jmax = q == 0 ? 0u : q == 1 ? 1u : q == 2 ? 2u : q == 3 ? 5u : q == 4 ? 11u : q == 5 ? 22u : q == 6 ? 44u
+                            : q == 7 ? 88u : q == 8 ? 177u : q == 9 ? 354u : 709u;       // floor(2^q * ln 2)
+    return j <= jmax ? n : k;
+}
+
 __device__ __forceinline__ const DevJob& find_job(const KParams& P, unsigned int tile) {
     int lo = 0, hi = P.njobs - 1;
     while (lo < hi) {                      // last job with tile_begin <= tile
@@ -342,12 +371,7 @@ struct Emitter {
             s = __dadd_rn(s, dither_noise(P.dither, (unsigned long long)f, (uint32_t)ch, key));
         else if (P.dither == 'F' && J.fpd) {                    // Dither::fpdither  rd/dither.rs:102-110
             const uint32_t fpd = J.fpd[(long long)ch * J.fpd_stride + fj];
-            const double l2 = floor(log2(fabs(s)));
-            int e;                                              // Rust `as i32`: NaN -> 0, saturating
-            if (l2 != l2) e = 0;
-            else if (l2 <= -2147483648.0) e = INT_MIN;
-            else if (l2 >= 2147483647.0) e = INT_MAX;
-            else e = (int)l2;
+            const int e = fpd_exponent(s);
             long long e2 = (long long)e + 62;
             e2 = e2 > 4096 ? 4096 : (e2 < -4096 ? -4096 : e2);   // 2^e2 is 0 / inf beyond the f64 range either way
             s = __dadd_rn(s, __dmul_rn(__dmul_rn((double)fpd, 3.4e-36), ldexp(1.0, (int)e2)));
@@ -1099,6 +1123,16 @@ __global__ void __launch_bounds__(256) fpd_kernel(const __grid_constant__ KParam
         s ^= s << 13; s ^= s >> 17; s ^= s << 5;
         *dst++ = s;
     }
+}
+
+// diagnostic: the octave step of the float dither on a vector of samples (tests/test_fpd_octave.py)
+__global__ void fpd_exponent_kernel(const double* __restrict__ s, int n, int* __restrict__ e) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) e[i] = fpd_exponent(s[i]);
+}
+cudaError_t launch_fpd_exponent(const double* d_s, int n, int* d_e, cudaStream_t stream) {
+    if (n > 0) fpd_exponent_kernel<<<(n + 255) / 256, 256, 0, stream>>>(d_s, n, d_e);
+    return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -29,6 +29,7 @@ const char* kernel_name(bool lm);
 void lutfir_set_shape(int bpo, int* F, int* DW);          // frames per lane set / word distance the kernels are built for
 int max_ctas_per_sm(bool lm, int threads, size_t smem);   // occupancy of the kernel at this geometry (0 on error)
 int kernel_variant(const KParams& P, bool lm, bool fast_writer_ok);   // which instantiation a launch uses
+cudaError_t launch_fpd_exponent(const double* d_s, int n, int* d_e, cudaStream_t stream);   // diagnostic
 cudaError_t launch_fpd(const KParams& P, cudaStream_t stream);     // per-sample xorshift32 states for dither F
 cudaError_t launch_kernels(const KParams& P, int variant, int grid, int threads, size_t smem, cudaStream_t stream);
 

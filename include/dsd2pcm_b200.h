@@ -217,6 +217,12 @@ typedef struct d2p_block_job {
 } d2p_block_job;
 int  d2p_batch_run_blocks(d2p_batch* b, const d2p_block_job* jobs, int njobs, void* cuda_stream);
 
+/* ---- diagnostics --------------------------------------------------------------------------------- */
+/* The octave step of the float dither, `s.abs().log2().floor() as i32` (Dither::fpdither, rd/dither.rs:102-104), as
+ * the kernels evaluate it, on n host samples: exponents[i] receives the value for samples[i].  Exists so that the one
+ * libm-dependent expression of the path can be compared with the host's libm at the octave boundaries. */
+int  d2p_debug_fpd_exponent(const double* samples, int n, int32_t* exponents, int device);
+
 #ifdef __cplusplus
 }
 #endif

@@ -221,6 +221,8 @@ extern "C" {
     pub fn d2p_block_range(cfg: *const d2p_config, payload_bytes: u64, first_frame: u64, frame_count: u64,
                            in_offset: *mut u64, in_bytes: *mut u64) -> c_int;
     pub fn d2p_batch_run_blocks(b: *mut d2p_batch, jobs: *const d2p_block_job, njobs: c_int, cuda_stream: *mut c_void) -> c_int;
+    // diagnostic: Dither::fpdither's `log2().floor() as i32` as the kernels evaluate it   rd/dither.rs:102-104
+    pub fn d2p_debug_fpd_exponent(samples: *const f64, n: c_int, exponents: *mut i32, device: c_int) -> c_int;
 
     // DsdReader::from_container (crate dsd-reader; call sites rd/lib.rs:92-99, 171-183)
     pub fn d2p_container_parse(bytes: *const u8, nbytes: usize, file_bytes: u64, info: *mut d2p_container_info) -> c_int;

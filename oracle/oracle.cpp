@@ -832,6 +832,17 @@ size_t orc_decimfir_run(const char* table, size_t decim, const double* in, size_
 
 // Scalar pieces of the writer, for unit tests
 int64_t orc_my_round(double x) { return PcmWriter::my_round(x); }
+// Dither::fpdither's octave step on a vector (rd/dither.rs:102-104): the host libm's log2, as in process_samp above
+void orc_fpd_exponent(const double* s, int n, int32_t* e) {
+    for (int i = 0; i < n; ++i) {
+        const double l2 = std::floor(std::log2(std::fabs(s[i])));
+        if (std::isnan(l2)) e[i] = 0;
+        else if (l2 <= -2147483648.0) e[i] = INT32_MIN;
+        else if (l2 >= 2147483647.0) e[i] = INT32_MAX;
+        else e[i] = (int)l2;
+    }
+}
+
 double orc_scale_factor(int bits, double level_db, uint32_t up) {
     Dither d('X', 0, false, 0);
     PcmWriter w(bits, true, level_db, d, 1, 1, up);
