@@ -300,12 +300,14 @@ def write_flac_file(path, bits, channels, rate, payload, frames, comments=()):
 
 def convert_file(in_path, out_path, out_rate=352800, filt="E", bits=24, dither="X", level_db=0.0, container="W",
                  dither_seed=0, device=0, dsf_stop_at_sample_count=False, raw_channels=2, raw_layout="P",
-                 raw_lsb_first=True, raw_dsd_rate=1, raw_block_size=4096, cancel_flag=None, progress=None):
+                 raw_lsb_first=True, raw_dsd_rate=1, raw_block_size=4096, cancel_flag=None, progress=None,
+                 copy_tags=False, append_rate=False):
     """One DSF / DSDIFF / raw DSD file -> one PCM file on the GPU (d2p_convert_file[_ex]).  Returns a dict.
     cancel_flag: ctypes.c_int32 that may be raised while the call runs; progress(frames_done, frames_total)."""
     opt = _capi.FileOptions(out_rate, ord(filt), bits, ord(dither), level_db, ord(container), dither_seed, device,
                             1 if dsf_stop_at_sample_count else 0, raw_channels, ord(raw_layout),
-                            1 if raw_lsb_first else 0, raw_dsd_rate, raw_block_size)
+                            1 if raw_lsb_first else 0, raw_dsd_rate, raw_block_size, 1 if copy_tags else 0,
+                            1 if append_rate else 0)
     res = _capi.FileResult()
     if cancel_flag is None and progress is None:
         _capi.check(_capi.lib().d2p_convert_file(C.byref(opt), str(in_path).encode(), str(out_path).encode(), C.byref(res)))
@@ -314,4 +316,17 @@ def convert_file(in_path, out_path, out_rate=352800, filt="E", bits=24, dither="
         _capi.check(_capi.lib().d2p_convert_file_ex(C.byref(opt), str(in_path).encode(), str(out_path).encode(), C.byref(res),
                                                     C.byref(cancel_flag) if cancel_flag is not None else None, cb, None))
     return {"in": _info_dict(res.info), "frames": int(res.frames), "out_bytes": int(res.out_bytes),
-            "clipped_samples": int(res.clipped_samples), "peak_abs": float(res.peak_abs), "dither_seed": int(res.dither_seed)}
+            "clipped_samples": int(res.clipped_samples), "peak_abs": float(res.peak_abs), "dither_seed": int(res.dither_seed),
+            "tag_bytes": int(res.tag_bytes)}
+
+
+def id3_to_vorbis(blob):
+    """ID3v2.3 / 2.4 tag bytes -> list of "KEY=value" Vorbis comments (d2p_id3_to_vorbis); None if the tag does not parse."""
+    blob = bytes(blob)
+    need = C.c_size_t()
+    n = _capi.lib().d2p_id3_to_vorbis(blob, len(blob), None, 0, C.byref(need))
+    if n < 0:
+        return None
+    buf = C.create_string_buffer(need.value)
+    _capi.lib().d2p_id3_to_vorbis(blob, len(blob), buf, need.value, C.byref(need))
+    return [x.decode("utf-8") for x in buf.raw[:need.value].split(b"\0") if x]

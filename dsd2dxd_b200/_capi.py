@@ -67,13 +67,20 @@ class FileOptions(C.Structure):
         ("level_db", C.c_double), ("out_container", C.c_int32), ("dither_seed", C.c_uint64), ("device", C.c_int32),
         ("dsf_stop_at_sample_count", C.c_int32),
         ("raw_channels", C.c_int32), ("raw_layout", C.c_int32), ("raw_lsb_first", C.c_int32), ("raw_dsd_rate", C.c_int32),
-        ("raw_block_size", C.c_uint32),
+        ("raw_block_size", C.c_uint32), ("copy_tags", C.c_int32), ("append_rate", C.c_int32),
     ]
 
 
 class FileResult(C.Structure):
     _fields_ = [("info", ContainerInfo), ("frames", C.c_uint64), ("out_bytes", C.c_uint64),
-                ("clipped_samples", C.c_int64), ("peak_abs", C.c_double), ("dither_seed", C.c_uint64)]
+                ("clipped_samples", C.c_int64), ("peak_abs", C.c_double), ("dither_seed", C.c_uint64),
+                ("tag_bytes", C.c_uint64)]
+
+
+class FlacPicture(C.Structure):
+    _fields_ = [("type", C.c_int32), ("mime", C.c_char_p), ("description", C.c_char_p), ("width", C.c_uint32),
+                ("height", C.c_uint32), ("depth", C.c_uint32), ("colors", C.c_uint32), ("data", C.c_void_p),
+                ("data_bytes", C.c_uint64)]
 
 
 # every symbol include/dsd2pcm_b200.h and include/dsd2pcm_b200_files.h declare
@@ -84,7 +91,7 @@ EXPORTS = [
     "d2p_convert_host", "d2p_check_level", "d2p_host_alloc", "d2p_host_free",
     "d2p_batch_create", "d2p_batch_destroy", "d2p_batch_run", "d2p_batch_convert_host", "d2p_batch_launches",
     "d2p_batch_stats", "d2p_batch_stats_reset", "d2p_batch_job_stats", "d2p_batch_set_control", "d2p_total_frames", "d2p_block_range", "d2p_batch_run_blocks", "d2p_debug_fpd_exponent",
-    "d2p_container_parse", "d2p_container_open", "d2p_pcm_header", "d2p_write_pcm_file", "d2p_write_flac_file", "d2p_convert_file", "d2p_convert_file_ex",
+    "d2p_container_parse", "d2p_container_open", "d2p_pcm_header", "d2p_write_pcm_file", "d2p_write_flac_file", "d2p_write_flac_file_ex", "d2p_id3_to_vorbis", "d2p_convert_file", "d2p_convert_file_ex",
 ]
 
 _lib = None
@@ -152,6 +159,9 @@ def lib():
     L.d2p_pcm_header.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint64, vp, C.c_size_t]
     L.d2p_write_pcm_file.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_uint32, vp, C.c_uint64]
     L.d2p_write_flac_file.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_uint32, vp, C.c_uint64, C.POINTER(C.c_char_p), C.c_int]
+    L.d2p_write_flac_file_ex.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_uint32, vp, C.c_uint64, C.POINTER(C.c_char_p), C.c_int,
+                                         C.POINTER(FlacPicture), C.c_int]
+    L.d2p_id3_to_vorbis.argtypes = [vp, C.c_size_t, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]
     L.d2p_convert_file.argtypes = [C.POINTER(FileOptions), C.c_char_p, C.c_char_p, C.POINTER(FileResult)]
     L.d2p_convert_file_ex.argtypes = [C.POINTER(FileOptions), C.c_char_p, C.c_char_p, C.POINTER(FileResult),
                                       C.POINTER(C.c_int32), PROGRESS_FN, vp]

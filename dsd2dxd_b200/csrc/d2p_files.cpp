@@ -18,8 +18,16 @@
 
 #include "../../include/dsd2pcm_b200_files.h"
 
-namespace d2p { int api_set_error(int st, const char* msg); }   // d2p_api.cu: thread-local d2p_last_error()
+namespace d2p { int api_set_error(int st, const char* msg);
+// d2p_tags.cpp
+bool tag_usable(const uint8_t* blob, size_t n);
+bool tag_append_album(std::vector<uint8_t>* blob, const char* suffix);
+void tag_to_flac(const uint8_t* blob, size_t n, std::vector<std::string>* comments, std::vector<d2p_flac_picture>* pics,
+                 std::vector<std::vector<uint8_t>>* storage, std::vector<std::string>* strings); }   // d2p_api.cu: thread-local d2p_last_error()
 using d2p::api_set_error;
+using d2p::tag_usable;
+using d2p::tag_append_album;
+using d2p::tag_to_flac;
 
 namespace {
 
@@ -285,6 +293,26 @@ int d2p_write_pcm_file(const char* path, int container, int bits, int channels, 
     return D2P_OK;
 }
 
+// The tag as an "ID3 " chunk behind the sample data of a RIFF / FORM file (what Tag::write_to_path does for WAV and
+// AIFF files): chunk id, size (little-endian in RIFF, big-endian in FORM), blob, pad byte to an even length; the
+// container's own size field grows by the same amount.
+static int append_id3_chunk(const char* path, bool riff, const std::vector<uint8_t>& tag) {
+    FileCloser f{std::fopen(path, "rb+")};
+    if (!f.f) return api_set_error(D2P_ERR_INVALID_ARG, "cannot reopen the output file for the tag chunk");
+    uint8_t head[8];
+    if (std::fread(head, 1, 8, f.f) != 8) return api_set_error(D2P_ERR_INVALID_ARG, "short output file");
+    const uint32_t n = (uint32_t)tag.size(), padded = (n + 1) & ~1u;
+    uint32_t total = riff ? le32(head + 4) : be32(head + 4);
+    total += 8 + padded;
+    uint8_t ch[8] = {'I', 'D', '3', ' ', 0, 0, 0, 0}, sz[4];
+    for (int i = 0; i < 4; ++i) { ch[4 + i] = (uint8_t)(riff ? n >> (8 * i) : n >> (8 * (3 - i))); sz[i] = (uint8_t)(riff ? total >> (8 * i) : total >> (8 * (3 - i))); }
+    const uint8_t zero = 0;
+    if (std::fseek(f.f, 0, SEEK_END) != 0 || std::fwrite(ch, 1, 8, f.f) != 8 || std::fwrite(tag.data(), 1, n, f.f) != n ||
+        (padded != n && std::fwrite(&zero, 1, 1, f.f) != 1) || std::fseek(f.f, 4, SEEK_SET) != 0 || std::fwrite(sz, 1, 4, f.f) != 4)
+        return api_set_error(D2P_ERR_INVALID_ARG, "write failed");
+    return D2P_OK;
+}
+
 // The reference seeds its dither from the OS for every run (rand::thread_rng, rd/dither.rs:64-76).  A caller that
 // leaves dither_seed at 0 gets the same behaviour: a seed drawn from the OS entropy source mixed with a hash of the
 // input path, so that no two files share a noise sequence.  A non-zero seed is used as given (reproducible runs).
@@ -383,11 +411,42 @@ int d2p_convert_file_ex(const d2p_file_options* opt, const char* in_path, const 
         if (st != D2P_OK) return st;                               // nothing has been written yet
     }
     R.frames = frames;
-    st = d2p_write_pcm_file(out_path, opt->out_container, opt->bits, ci.channels, opt->out_rate, h_out, frames);
+    // ---- metadata carry-over (save_output, rd/conversion_context.rs:565-590) ----
+    std::vector<uint8_t> id3;
+    if (opt->copy_tags && ci.id3_offset && ci.id3_bytes >= 10 && ci.id3_bytes < (64u << 20)) {
+        id3.resize((size_t)ci.id3_bytes);
+        if (std::fseek(fc.f, (long)ci.id3_offset, SEEK_SET) != 0 || std::fread(id3.data(), 1, id3.size(), fc.f) != id3.size() ||
+            !tag_usable(id3.data(), id3.size()))
+            id3.clear();                                           // "Input file has no id3; skipping id3 copy."
+    }
+    if (!id3.empty() && opt->append_rate) {
+        const char* dot = nullptr;                                 // abbrev_rate_pair :603-621
+        switch (opt->out_rate) {
+        case 88200: dot = " [88.2K]"; break; case 96000: dot = " [96K]"; break; case 176400: dot = " [176.4K]"; break;
+        case 192000: dot = " [192K]"; break; case 352800: dot = " [352.8K]"; break; case 384000: dot = " [384K]"; break;
+        case 705600: dot = " [705.6K]"; break; case 1411200: dot = " [1411.2K]"; break; default: break;
+        }
+        if (dot) tag_append_album(&id3, dot);
+    }
+    if (opt->out_container == D2P_FILE_FLAC && !id3.empty()) {
+        std::vector<std::string> comments, strings;
+        std::vector<d2p_flac_picture> pics;
+        std::vector<std::vector<uint8_t>> storage;
+        tag_to_flac(id3.data(), id3.size(), &comments, &pics, &storage, &strings);
+        std::vector<const char*> cptr;
+        for (const std::string& c : comments) cptr.push_back(c.c_str());
+        st = d2p_write_flac_file_ex(out_path, opt->bits, ci.channels, opt->out_rate, h_out, frames, cptr.data(), (int)cptr.size(),
+                                    pics.data(), (int)pics.size());
+    } else {
+        st = d2p_write_pcm_file(out_path, opt->out_container, opt->bits, ci.channels, opt->out_rate, h_out, frames);
+        if (st == D2P_OK && !id3.empty() && opt->out_container != D2P_FILE_RAW && opt->out_container != D2P_FILE_FLAC)
+            st = append_id3_chunk(out_path, opt->out_container == D2P_FILE_WAV, id3);
+    }
     if (st != D2P_OK) {                                            // no partly written file is left behind
         if (std::strncmp(out_path, "/dev/", 5) != 0) std::remove(out_path);
         return st;
     }
+    R.tag_bytes = id3.size();
     if (opt->out_container == D2P_FILE_FLAC) {                     // compressed: the size is whatever the encoder produced
         FileCloser of{std::fopen(out_path, "rb")};
         if (of.f && std::fseek(of.f, 0, SEEK_END) == 0) R.out_bytes = (uint64_t)std::ftell(of.f);
@@ -396,6 +455,7 @@ int d2p_convert_file_ex(const d2p_file_options* opt, const char* in_path, const 
     Bytes h;
     build_header(opt->out_container, opt->bits, ci.channels, opt->out_rate, frames, &h);
     R.out_bytes = h.v.size() + frames * (uint64_t)ci.channels * (uint64_t)pi.bytes_per_sample;
+    if (!id3.empty() && opt->out_container != D2P_FILE_RAW) R.out_bytes += 8 + ((id3.size() + 1) & ~(size_t)1);
     return D2P_OK;
 }
 

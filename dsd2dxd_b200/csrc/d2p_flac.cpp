@@ -330,7 +330,12 @@ void unpack(const uint8_t* p, int bits, int C, size_t first, int n, std::vector<
 
 extern "C" int d2p_write_flac_file(const char* path, int bits, int channels, uint32_t rate, const void* payload, uint64_t frames,
                                    const char* const* comments, int n_comments) {
-    if (!path || (!payload && frames) || n_comments < 0 || (n_comments && !comments))
+    return d2p_write_flac_file_ex(path, bits, channels, rate, payload, frames, comments, n_comments, nullptr, 0);
+}
+
+extern "C" int d2p_write_flac_file_ex(const char* path, int bits, int channels, uint32_t rate, const void* payload, uint64_t frames,
+                                      const char* const* comments, int n_comments, const d2p_flac_picture* pictures, int n_pictures) {
+    if (!path || (!payload && frames) || n_comments < 0 || (n_comments && !comments) || n_pictures < 0 || (n_pictures && !pictures))
         return api_set_error(D2P_ERR_INVALID_ARG, "null argument");
     if (channels <= 0) return api_set_error(D2P_ERR_INVALID_ARG, "No channels");
     if (channels > 8) return api_set_error(D2P_ERR_INVALID_ARG, "FLAC: at most 8 channels");
@@ -344,7 +349,7 @@ extern "C" int d2p_write_flac_file(const char* path, int bits, int channels, uin
     FileCloser fc{std::fopen(path, "wb+")};
     if (!fc.f) return api_set_error(D2P_ERR_INVALID_ARG, (std::string("cannot create ") + path).c_str());
 
-    // "fLaC", STREAMINFO (rewritten at the end), VORBIS_COMMENT (last)
+    // "fLaC", STREAMINFO (rewritten at the end), VORBIS_COMMENT, PICTURE blocks; the last one carries the end flag
     std::vector<uint8_t> head;
     auto be = [&](uint64_t x, int nbytes) { for (int i = nbytes - 1; i >= 0; --i) head.push_back((uint8_t)(x >> (8 * i))); };
     auto le32 = [&](uint32_t x) { for (int i = 0; i < 4; ++i) head.push_back((uint8_t)(x >> (8 * i))); };
@@ -356,12 +361,25 @@ extern "C" int d2p_write_flac_file(const char* path, int bits, int channels, uin
     size_t vc = 4 + vendor.size() + 4;
     for (int i = 0; i < n_comments; ++i) vc += 4 + std::strlen(comments[i]);
     if (vc >= (1u << 24)) return api_set_error(D2P_ERR_INVALID_ARG, "FLAC: comment block too large");
-    be(0x80 | 4, 1); be(vc, 3);
+    be((n_pictures ? 0x00 : 0x80) | 4, 1); be(vc, 3);
     le32((uint32_t)vendor.size()); head.insert(head.end(), vendor.begin(), vendor.end());
     le32((uint32_t)n_comments);
     for (int i = 0; i < n_comments; ++i) {
         const size_t L = std::strlen(comments[i]);
         le32((uint32_t)L); head.insert(head.end(), comments[i], comments[i] + L);
+    }
+    for (int i = 0; i < n_pictures; ++i) {                         // METADATA_BLOCK_PICTURE: all fields big-endian
+        const d2p_flac_picture& p = pictures[i];
+        const size_t ml = p.mime ? std::strlen(p.mime) : 0, dl = p.description ? std::strlen(p.description) : 0;
+        const uint64_t sz = 32 + ml + dl + p.data_bytes;
+        if (sz >= (1u << 24)) return api_set_error(D2P_ERR_INVALID_ARG, "FLAC: picture block too large");
+        be((i == n_pictures - 1 ? 0x80 : 0x00) | 6, 1); be(sz, 3);
+        be((uint32_t)p.type, 4);
+        be(ml, 4); head.insert(head.end(), p.mime, p.mime + ml);
+        be(dl, 4); head.insert(head.end(), p.description, p.description + dl);
+        be(p.width, 4); be(p.height, 4); be(p.depth, 4); be(p.colors, 4);
+        be(p.data_bytes, 4);
+        head.insert(head.end(), (const uint8_t*)p.data, (const uint8_t*)p.data + p.data_bytes);
     }
     if (std::fwrite(head.data(), 1, head.size(), fc.f) != head.size()) return api_set_error(D2P_ERR_INVALID_ARG, "write failed");
 

@@ -17,7 +17,10 @@
  *   flac     AudioFile::save_flac_file   rd/audio_file.rs:454-573   (which integers go in: 16 / 20 / 24 bit, float
  *            written as 24 bit; the bitstream is the encoder's own -- the reference delegates it to the
  *            flac-codec crate -- and is checked by decode equality)
- * ID3 -> tag mapping and output naming stay out of scope.
+ *   tags     PcmWriter::id3_to_flac_meta, ConversionContext::save_output / append_album_suffix
+ *            rd/pcm_writer.rs:30-96, 425-605, rd/conversion_context.rs:565-621   (crates id3 1.16.3 and flac-codec are not
+ *            in the mount: field mapping per the reference's tables, chunk bytes unpinned).  Output naming, output
+ *            directories and artwork copying are the caller's business: tools/d2p_cli.cpp does them like the reference.
  */
 #ifndef DSD2PCM_B200_FILES_H
 #define DSD2PCM_B200_FILES_H
@@ -72,6 +75,22 @@ int d2p_write_pcm_file(const char* path, int container, int bits, int channels, 
  * block (may be NULL / 0).  Lossless: decoding returns exactly those integers; STREAMINFO carries their MD5. */
 int d2p_write_flac_file(const char* path, int bits, int channels, uint32_t rate, const void* payload, uint64_t frames,
                         const char* const* comments, int n_comments);
+/* One FLAC PICTURE block (PcmWriter::add_picture, rd/pcm_writer.rs:583-603: front cover = 3, back cover = 4). */
+typedef struct d2p_flac_picture {
+    int32_t     type;
+    const char* mime;
+    const char* description;   /* UTF-8 */
+    uint32_t    width, height, depth, colors;
+    const void* data;
+    uint64_t    data_bytes;
+} d2p_flac_picture;
+int d2p_write_flac_file_ex(const char* path, int bits, int channels, uint32_t rate, const void* payload, uint64_t frames,
+                           const char* const* comments, int n_comments, const d2p_flac_picture* pictures, int n_pictures);
+/* ID3v2.3 / 2.4 tag blob -> Vorbis comments, field for field like PcmWriter::id3_to_flac_meta (rd/pcm_writer.rs:30-96,
+ * 425-580): "KEY=value" strings in the reference's insertion order, UTF-8, each NUL-terminated, the list closed by an
+ * empty string.  Returns the number of comments (-1 if the blob does not parse, as for the truncated tags of the
+ * *brokenid3* fixtures); *needed = bytes the list takes; nothing is written unless cap >= *needed. */
+int d2p_id3_to_vorbis(const uint8_t* id3, size_t nbytes, char* out, size_t cap, size_t* needed);
 
 typedef struct d2p_file_options {
     uint32_t out_rate;        /* -r */
@@ -87,6 +106,12 @@ typedef struct d2p_file_options {
     /* raw input (.dsd / anything that is not DSF or DSDIFF): the CLI's -c -f -e -s -i */
     int32_t  raw_channels, raw_layout, raw_lsb_first, raw_dsd_rate;
     uint32_t raw_block_size;
+    /* metadata carry-over (ConversionContext::save_output, rd/conversion_context.rs:565-590).  The reference always does
+     * it when the input has a readable ID3v2 tag; here it is a switch (0 = bare PCM file, as before):
+     *   FLAC: Vorbis comments + front / back cover PICTURE blocks from the tag (id3_to_flac_meta);
+     *   WAV / AIFF / AIFC: the tag copied into an "ID3 " chunk behind the sample data (tag.write_to_path). */
+    int32_t  copy_tags;
+    int32_t  append_rate;     /* -a: " [<rate>]" appended to the album title (append_album_suffix :592-601) */
 } d2p_file_options;
 
 typedef struct d2p_file_result {
@@ -96,6 +121,7 @@ typedef struct d2p_file_result {
     int64_t  clipped_samples;
     double   peak_abs;
     uint64_t dither_seed;     /* the seed the conversion used (see d2p_file_options.dither_seed) */
+    uint64_t tag_bytes;       /* size of the ID3v2 tag carried over (0: none, unreadable, or copy_tags off) */
 } d2p_file_result;
 
 /* One input file -> one PCM file: parse the container, stream the payload through the GPU

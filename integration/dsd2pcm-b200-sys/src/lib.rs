@@ -153,6 +153,8 @@ pub struct d2p_file_options {
     pub raw_lsb_first: i32,
     pub raw_dsd_rate: i32,
     pub raw_block_size: u32,
+    pub copy_tags: i32,
+    pub append_rate: i32,
 }
 
 #[repr(C)]
@@ -164,6 +166,22 @@ pub struct d2p_file_result {
     pub clipped_samples: i64,
     pub peak_abs: f64,
     pub dither_seed: u64,
+    pub tag_bytes: u64,
+}
+
+/// One FLAC PICTURE block (front cover = 3, back cover = 4)   rd/pcm_writer.rs:583-603
+#[repr(C)]
+#[derive(Clone, Copy, Debug)]
+pub struct d2p_flac_picture {
+    pub r#type: i32,
+    pub mime: *const c_char,
+    pub description: *const c_char,
+    pub width: u32,
+    pub height: u32,
+    pub depth: u32,
+    pub colors: u32,
+    pub data: *const c_void,
+    pub data_bytes: u64,
 }
 
 /// `progress` of d2p_batch_set_control / d2p_convert_file_ex: (user, frames_done, frames_total)
@@ -235,6 +253,11 @@ extern "C" {
     pub fn d2p_write_flac_file(path: *const c_char, bits: c_int, channels: c_int, rate: u32, payload: *const c_void, frames: u64,
                                comments: *const *const c_char, n_comments: c_int) -> c_int;
     // Rdsd2Pcm::from_container + do_conversion + PcmWriter::save_file   rd/lib.rs:171-182, 275-281, rd/pcm_writer.rs:300-318
+    pub fn d2p_write_flac_file_ex(path: *const c_char, bits: c_int, channels: c_int, rate: u32, payload: *const c_void, frames: u64,
+                                  comments: *const *const c_char, n_comments: c_int, pictures: *const d2p_flac_picture,
+                                  n_pictures: c_int) -> c_int;
+    // PcmWriter::id3_to_flac_meta   rd/pcm_writer.rs:425-580
+    pub fn d2p_id3_to_vorbis(id3: *const u8, nbytes: usize, out: *mut c_char, cap: usize, needed: *mut usize) -> c_int;
     pub fn d2p_convert_file(opt: *const d2p_file_options, in_path: *const c_char, out_path: *const c_char,
                             res: *mut d2p_file_result) -> c_int;
     pub fn d2p_convert_file_ex(opt: *const d2p_file_options, in_path: *const c_char, out_path: *const c_char,

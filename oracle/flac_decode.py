@@ -144,7 +144,7 @@ def decode(data):
         raise FlacError("no fLaC marker")
     pos = 4
     info = None
-    vendor, comments = None, []
+    vendor, comments, pictures = None, [], []
     while True:
         hdr = data[pos]
         size = int.from_bytes(data[pos + 1:pos + 4], "big")
@@ -173,6 +173,19 @@ def decode(data):
                 q += 4 + n
             if q != size:
                 raise FlacError("VORBIS_COMMENT length mismatch")
+        elif kind == 6:                                            # PICTURE: big-endian fields
+            ptype, ml = struct.unpack_from(">II", body, 0)
+            mime = body[8:8 + ml].decode("ascii")
+            q = 8 + ml
+            dl = struct.unpack_from(">I", body, q)[0]
+            desc = body[q + 4:q + 4 + dl].decode("utf-8")
+            q += 4 + dl
+            w, h, depth, colors, n = struct.unpack_from(">IIIII", body, q)
+            q += 20
+            if q + n != size:
+                raise FlacError("PICTURE length mismatch")
+            pictures.append({"type": ptype, "mime": mime, "description": desc, "width": w, "height": h, "depth": depth,
+                             "colors": colors, "data": body[q:q + n]})
         elif kind == 127:
             raise FlacError("invalid metadata block type")
         pos += 4 + size
@@ -266,6 +279,6 @@ def decode(data):
             inter += (chans[c][i] & ((1 << (8 * nbytes)) - 1)).to_bytes(nbytes, "little")
     h.update(bytes(inter))
     out = dict(info)
-    out.update(samples=chans, vendor=vendor, comments=comments, md5_ok=h.digest() == info["md5"], frames=nframes,
+    out.update(samples=chans, vendor=vendor, comments=comments, pictures=pictures, md5_ok=h.digest() == info["md5"], frames=nframes,
                frame_sizes=sizes)
     return out

@@ -90,7 +90,7 @@ def test_rust_ffi_crate_declares_exactly_the_header_functions():
 
 
 C_TO_RUST = {"int32_t": "i32", "uint32_t": "u32", "int64_t": "i64", "uint64_t": "u64", "double": "f64", "float": "f32",
-             "const void*": "*const c_void", "void*": "*mut c_void", "double*": "*mut f64", "d2p_container_info": "d2p_container_info"}
+             "const void*": "*const c_void", "void*": "*mut c_void", "const char*": "*const c_char", "double*": "*mut f64", "d2p_container_info": "d2p_container_info"}
 
 
 def _c_struct_fields(name):
@@ -100,7 +100,7 @@ def _c_struct_fields(name):
         decl = " ".join(decl.split())
         if not decl:
             continue
-        m = re.match(r"(const void\*|void\*|double\*|[a-z0-9_]+)\s+(.*)", decl)
+        m = re.match(r"(const void\*|const char\*|void\*|double\*|[a-z0-9_]+)\s+(.*)", decl)
         ctype, names = m.group(1), m.group(2)
         for nm in names.split(","):
             nm = nm.strip()
@@ -111,16 +111,16 @@ def _c_struct_fields(name):
 
 def _rust_struct_fields(name):
     body = re.search(r"pub struct %s \{(.*?)\n\}" % name, _rust(), flags=re.S).group(1)
-    return [(m.group(1), m.group(2).strip()) for m in re.finditer(r"pub (\w+): ([^,\n]+),", body)]
+    return [(m.group(1), m.group(2).strip()) for m in re.finditer(r"pub ((?:r#)?\w+): ([^,\n]+),", body)]
 
 
 @pytest.mark.parametrize("name", ["d2p_config", "d2p_plan_info", "d2p_job", "d2p_block_job", "d2p_container_info",
-                                  "d2p_file_options", "d2p_file_result"])
+                                  "d2p_file_options", "d2p_file_result", "d2p_flac_picture"])
 def test_rust_structs_mirror_the_c_layout(name):
     cf, rf = _c_struct_fields(name), _rust_struct_fields(name)
     assert len(cf) == len(rf), (cf, rf)
     for (cn, ct, arr), (rn, rt) in zip(cf, rf):
-        assert rn == cn or (cn, rn) == ("in", "input")          # `in` is a Rust keyword
+        assert rn == cn or (cn, rn) in (("in", "input"), ("type", "r#type"))      # Rust keywords
         if ct == "char":
             want = "c_char"
         else:

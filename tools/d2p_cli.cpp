@@ -22,6 +22,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <filesystem>
+#include <fstream>
 #include <string>
 #include <vector>
 
@@ -118,6 +120,24 @@ static std::string out_name(const Cli& c, const std::string& in) {   // get_out_
     return name + "." + ext;
 }
 
+// copy_artwork (rd/conversion_context.rs:479-533): with -p, every .jpg / .jpeg / .png of the input's directory is copied
+// next to the output unless a file of that name is already there
+static void copy_artwork(const Cli& c, const std::string& in, const std::string& out) {
+    namespace fs = std::filesystem;
+    if (c.out_dir.empty() || in == "-") return;
+    std::error_code ec;
+    const fs::path src = fs::path(in).parent_path().empty() ? fs::path(".") : fs::path(in).parent_path();
+    const fs::path dst = fs::path(out).parent_path();
+    for (const auto& e : fs::directory_iterator(src, ec)) {
+        if (!e.is_regular_file(ec)) continue;
+        std::string ext = e.path().extension().string();
+        for (char& ch : ext) ch = (char)std::tolower((unsigned char)ch);
+        if (ext != ".jpg" && ext != ".png" && ext != ".jpeg") continue;
+        const fs::path to = dst / e.path().filename();
+        if (!fs::exists(to, ec)) fs::copy_file(e.path(), to, fs::copy_options::none, ec);
+    }
+}
+
 static void report(const Cli& c, const std::string& file, double audio_s, double dsp_s, double total_s) {
     if (c.quiet) return;
     const size_t slash = file.find_last_of('/');
@@ -200,12 +220,15 @@ int main(int argc, char** argv) {
         o.dither_seed = c.seed; o.device = c.device;
         o.raw_channels = c.channels; o.raw_layout = c.format; o.raw_lsb_first = c.endian == 'L'; o.raw_dsd_rate = c.in_rate;
         o.raw_block_size = c.block;
+        o.copy_tags = 1;                        // the reference always carries a readable tag over (save_output :565-590)
+        o.append_rate = c.append ? 1 : 0;
         d2p_file_result r;
         const std::string out = c.output == 'S' ? "/dev/stdout" : out_name(c, f);
         const double t0 = now();
         const int st = d2p_convert_file_ex(&o, f.c_str(), out.c_str(), &r, &g_cancel, nullptr, nullptr);
         const double dt = now() - t0;
         if (st != D2P_OK) { std::fprintf(stderr, "d2p_cli: %s: %s\n", f.c_str(), st == D2P_ERR_CANCELLED ? "cancelled" : d2p_last_error()); ++failed; continue; }
+        if (c.output != 'S') copy_artwork(c, f, out);
         const double audio = (double)r.in.data_bytes / r.in.channels * 8.0 / (double)r.in.sample_rate;
         report(c, f, audio, dt, dt);
         if (!c.quiet && r.clipped_samples) std::fprintf(stderr, "%lld samples clipped\n", (long long)r.clipped_samples);
