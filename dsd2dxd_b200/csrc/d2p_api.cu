@@ -108,41 +108,21 @@ static LmLut lm_lut_layout(const Plan& p) {
     return l;
 }
 
-// Row pitch (in doubles, mod 16) of a phase-major tile with D rows that lets `lanes` consecutive samples -- row
-// e mod D, column e div D -- be stored by one half-warp without two lanes in the same 8-byte bank pair, whatever row
-// the half-warp starts in.  Readers walk along a row (consecutive lanes = consecutive columns), so any pitch suits them.
-static int lm_pitch_residue(int D, int lanes) {
-    int best = 1; long best_cost = -1;
-    for (int r = 0; r < 16; ++r) {
-        long cost = 0;
-        for (int r0 = 0; r0 < D; ++r0) {
-            int cnt[16] = {0}, worst = 0;
-            for (int u = 0; u < lanes; ++u) {
-                const int e = r0 + u, b = ((e % D) * r + e / D) & 15;
-                worst = std::max(worst, ++cnt[b]);
-            }
-            cost += worst;
-        }
-        if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = r; }
-    }
-    return best;
-}
-static int lm_pitch(long long min_pitch, int D, int lanes) {
-    const int r = lm_pitch_residue(D, lanes);
-    return (int)(min_pitch + ((r - min_pitch) % 16 + 16) % 16);
-}
+// Stage tiles are stored column by column: a column holds the D samples of one decimation period in Dp = D | 1
+// doubles (odd), so a tap walk is contiguous and the columns of neighbouring outputs fall into different bank pairs.
+static int lm_col_pitch(int D) { return D | 1; }
 
 static LmGeom lm_geometry(const Plan& p, const LmLut& ll, int TF, int NB) {
     LmGeom g;
     const int C = p.cfg.channels;
     const long long k2span = p.nstages == 3 ? (long long)(TF - 1) * p.D3 + (2 * p.h3 - 1) : (TF - 1);
     const long long cnt1 = k2span * p.D2 + (2 * p.h2 - 1) + 1;
-    g.pitch2 = lm_pitch((cnt1 + 2 * p.D2 - 1) / p.D2 + 2, p.D2, ll.A);     // + one column for the sigma shift
-    g.s1_cap = (p.D2 * g.pitch2 + 1) & ~1;
+    g.pitch2 = lm_col_pitch(p.D2);
+    g.s1_cap = (int)((((cnt1 + 2 * p.D2 - 1) / p.D2 + 2) * g.pitch2 + 1) & ~1LL);     // + one column for the sigma shift
     g.pitch3 = 0; g.s2_cap = 0;
     if (p.nstages == 3) {
-        g.pitch3 = lm_pitch((k2span + 1 + 2 * p.D3 - 1) / p.D3 + 2, p.D3, 16);
-        g.s2_cap = (p.D3 * g.pitch3 + 1) & ~1;
+        g.pitch3 = lm_col_pitch(p.D3);
+        g.s2_cap = (int)((((k2span + 1 + 2 * p.D3 - 1) / p.D3 + 2) * g.pitch3 + 1) & ~1LL);
     }
     const long long bits = cnt1 * p.m1 / p.L + 64 + p.m1;
     g.tile_stride = (int)round16((size_t)(bits / 8) + 16) + 48;

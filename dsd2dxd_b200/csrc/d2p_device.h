@@ -91,7 +91,7 @@ struct KParams {
     int inv_d2, inv_d3;       // ceil(65536 / D): (x * inv) >> 16 == x / D for the small x the kernels divide
     int s1_cap, s2_cap;       // doubles per channel slot of the stage-1 / stage-2 tiles
     int NB;                   // channel slots kept in flight together
-    int pitch2, pitch3;       // doubles per phase row of the phase-major stage-1 / stage-2 tiles
+    int pitch2, pitch3;       // doubles per column (one decimation period, padded to an odd count) of the stage-1 / stage-2 tiles
     int lm_cons;              // consumer threads of the lm_kernel instantiation in use (448 or 896)
     int lmA, lmGp, lm_cyc;    // active lanes per half-warp, LUT block pitch (slots, odd), phase patterns (1 or 2)
     long long lm_base_hi;     // high-rate index of stage-1 output 0

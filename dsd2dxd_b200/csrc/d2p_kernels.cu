@@ -803,42 +803,44 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
 // NB channels are kept in flight together so that stages 2/3, which have only TF-ish outputs per channel,
 // still occupy the whole CTA.
 // ------------------------------------------------------------------------------------------------
-// Direct symmetric FIR over a phase-major tile (DecimFIRSym::convolve_direct, rd/lm_resampler.rs:717-751).
-// Sample e of the tile lives at row (e + sigma) mod D, column (e + sigma) div D.  Tap k reads the front sample
-// e = T0 - k and the back sample e = k: the front address walks one row down per tap, the back address one row
-// up.  sigma = -h (mod D) makes both walkers wrap at the same taps (rows rf and D-1-rf), so the taps split into
-// a few straight runs.  `col` already points at this output's column.  All bookkeeping is warp-uniform.
-// N taps of one straight run, all operand loads ahead of the adds: the loads of a run are independent of the
-// accumulator chain, so the compiler may issue them back to back (software pipelining by full unrolling).
+// Direct symmetric FIR (DecimFIRSym::convolve_direct, rd/lm_resampler.rs:717-751) over a tile of the previous stage.
+// Tap k reads the front sample e = T0 - k and the back sample e = k.  sigma = -h (mod D) makes both walkers leave their
+// columns at the same taps, so the taps split into a few straight runs; `col` points at this output's column 0.  All
+// bookkeeping is warp-uniform.  N taps of one straight run, all operand loads ahead of the adds: the loads of a run are
+// independent of the accumulator chain, so the compiler may issue them back to back.
 template <int N>
-__device__ __forceinline__ double fir_run(const double* __restrict__ taps, const double*& pf, const double*& pb, int pitch,
-                                          double total) {
+__device__ __forceinline__ double fir_run(const double* __restrict__ taps, const double*& pf, const double*& pb, double total) {
     double f[N], b[N];
 #pragma unroll
-    for (int i = 0; i < N; ++i) { f[i] = *pf; b[i] = *pb; pf -= pitch; pb += pitch; }
+    for (int i = 0; i < N; ++i) { f[i] = pf[-i]; b[i] = pb[i]; }   // one address register per walker, immediate offsets
+    pf -= N; pb += N;
 #pragma unroll
     for (int i = 0; i < N; ++i) total = __dadd_rn(total, __dmul_rn(taps[i], __dadd_rn(f[i], b[i])));
     return total;
 }
 
+// Tile layout: sample e of the tile lives in column (e + sigma) div D at row (e + sigma) mod D, a column being Dp >= D
+// consecutive doubles (Dp odd).  A tap walk is therefore CONTIGUOUS in memory -- the front walker goes down one double
+// per tap, the back walker up -- and only skips the Dp - D pad slots when it leaves a column; the lanes of a half-warp
+// (consecutive outputs = consecutive columns) are Dp doubles apart, an odd stride, i.e. 16 different bank pairs.
 __device__ __forceinline__ double fir_sym_t(const double* __restrict__ taps, const double* __restrict__ col, int h, int D,
-                                            int pitch, int sigma, int rf0, int q0) {
+                                            int Dp, int sigma, int rf0, int q0) {
     // front element of tap 0 (T0 = 2h-1), shifted: ef = 2h-1+sigma, rf0 = ef mod D, q0 = ef div D (host-computed)
     int rf = rf0;
-    const double* pf = col + rf * pitch + q0;
-    const double* pb = col + sigma * pitch;                         // back element of tap 0: row sigma == D-1-rf, column 0
-    const int wrap = D * pitch - 1;
+    const double* pf = col + q0 * Dp + rf;
+    const double* pb = col + sigma;                                 // back element of tap 0: row sigma == D-1-rf, column 0
+    const int skip = Dp - D;
     double total = 0.0;
     int k = 0;
     while (k < h) {
-        int run = rf + 1;                                           // taps until both walkers leave the tile rows
+        int run = rf + 1;                                           // taps until both walkers leave their columns
         if (h - k < run) run = h - k;
         int i = 0;
-        for (; i + 7 <= run; i += 7) total = fir_run<7>(taps + k + i, pf, pb, pitch, total);   // D is 3, 7, 14 or 28
-        for (; i + 3 <= run; i += 3) total = fir_run<3>(taps + k + i, pf, pb, pitch, total);
-        for (; i < run; ++i) total = fir_run<1>(taps + k + i, pf, pb, pitch, total);
+        for (; i + 7 <= run; i += 7) total = fir_run<7>(taps + k + i, pf, pb, total);   // D is 3, 7, 14 or 28
+        for (; i + 3 <= run; i += 3) total = fir_run<3>(taps + k + i, pf, pb, total);
+        for (; i < run; ++i) total = fir_run<1>(taps + k + i, pf, pb, total);
         k += run;
-        rf = D - 1; pf += wrap; pb -= wrap;                         // front: previous column, top row; back: next column, row 0
+        rf = D - 1; pf -= skip; pb += skip;                         // front: bottom row of the previous column; back: row 0 of the next
     }
     return total;
 }
@@ -921,7 +923,7 @@ __global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __gri
     const int step_n = A * nhw;
     const int step_q = step_n / P.D2, step_ph = step_n - step_q * P.D2;
     const int step_t = (int)P.lm_step_t;                            // = m1 * A * nhw / L (exact)
-    const int step_el = step_ph * P.pitch2 + step_q, wrap_el = 1 - P.D2 * P.pitch2;
+    const int step_el = step_ph + step_q * P.pitch2, wrap_el = P.pitch2 - P.D2;   // next column: row -= D2
     const int own = A * hw + u;                                     // this thread's output offset from nA
     const int own_t = (P.m1 * own) / P.L;                           // ... and its input-time offset (nA has phase 0)
 
@@ -975,14 +977,15 @@ __global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __gri
                 if (u < A) {
                     for (int sl = 0; sl < nbc; ++sl) {
                         const uint32_t* tw = reinterpret_cast<const uint32_t*>(tiles + (size_t)(cb + sl) * P.tile_stride);
-                        double* pd = s1 + (size_t)sl * P.s1_cap + p0 * P.pitch2 + q0;
+                        double* pd = s1 + (size_t)sl * P.s1_cap + q0 * P.pitch2 + p0;
+                        const int sq = step_q * P.pitch2;
                         if (step_ph == 0 && relz <= rel0) {
                             // the usual case: a round advances a whole number of stage-2 periods (the lane's row of the
                             // phase-major tile never changes) and every output of the tile exists
                             // two outputs per round trip: both windows are fetched and all ten look-ups issued before the
                             // first store (stores to the stage-1 tile may alias the input tile as far as the compiler knows)
                             int rel = rel0, d = d0;
-                            for (; rel + step_n <= last_rel; rel += 2 * step_n, d += 2 * step_t, pd += 2 * step_q) {
+                            for (; rel + step_n <= last_rel; rel += 2 * step_n, d += 2 * step_t, pd += 2 * sq) {
                                 const int w0 = d >> 5, d1 = d + step_t, w1 = d1 >> 5;
                                 const uint32_t z0 = __brev(__funnelshift_r(tw[w0], tw[w0 + 1], d & 31));   // bit j = x[t-j]
                                 const uint32_t z1 = __brev(__funnelshift_r(tw[w1], tw[w1 + 1], d1 & 31));
@@ -991,7 +994,7 @@ __global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __gri
                                 if (GMAX > 2) { y0 = __dadd_rn(y0, lds_f64<16>(__dp2a_hi(rlo, z0, tpl))); y1 = __dadd_rn(y1, lds_f64<16>(__dp2a_hi(rlo, z1, tpl))); }
                                 if (GMAX > 3) { y0 = __dadd_rn(y0, lds_f64<24>(__dp2a_hi(rhi, z0, tpl))); y1 = __dadd_rn(y1, lds_f64<24>(__dp2a_hi(rhi, z1, tpl))); }
                                 if (GMAX > 4) { y0 = __dadd_rn(y0, lds_f64<32>(__dp2a_lo(rlo, z0, tpl))); y1 = __dadd_rn(y1, lds_f64<32>(__dp2a_lo(rlo, z1, tpl))); }
-                                pd[0] = y0; pd[step_q] = y1;
+                                pd[0] = y0; pd[sq] = y1;
                             }
                             if (rel <= last_rel) {
                                 const int w = d >> 5;
@@ -1030,12 +1033,12 @@ __global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __gri
                     while (idx >= cnt2) { idx -= cnt2; ++sl; }
                     double tot = 0.0;
                     if (H.k2_lo + idx >= 0)
-                        tot = fir_sym_t(P.c2, s1 + (size_t)sl * P.s1_cap + (idx + H.j2_0), P.h2, P.D2, P.pitch2, P.sigma2, P.fir2_rf, P.fir2_q);
+                        tot = fir_sym_t(P.c2, s1 + (size_t)sl * P.s1_cap + (idx + H.j2_0) * P.pitch2, P.h2, P.D2, P.pitch2, P.sigma2, P.fir2_rf, P.fir2_q);
                     if (P.nstages == 2) em.emit(P, J, ostage, cb + sl, f0 + idx, idx, tot);
                     else {
                         const int e3 = idx + P.sigma3;
                         const int qq = (e3 * P.inv_d3) >> 16;
-                        s2[(size_t)sl * P.s2_cap + (e3 - qq * P.D3) * P.pitch3 + qq] = tot;
+                        s2[(size_t)sl * P.s2_cap + qq * P.pitch3 + (e3 - qq * P.D3)] = tot;
                     }
                 }
                 // ---- stage 3 ----
@@ -1044,7 +1047,7 @@ __global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __gri
                     for (int item = tid; item < nbc * nf; item += NCONS) {
                         int sl = 0, idx = item;
                         while (idx >= nf) { idx -= nf; ++sl; }
-                        const double y = fir_sym_t(P.c3, s2 + (size_t)sl * P.s2_cap + idx, P.h3, P.D3, P.pitch3, P.sigma3, P.fir3_rf, P.fir3_q);
+                        const double y = fir_sym_t(P.c3, s2 + (size_t)sl * P.s2_cap + idx * P.pitch3, P.h3, P.D3, P.pitch3, P.sigma3, P.fir3_rf, P.fir3_q);
                         em.emit(P, J, ostage, cb + sl, f0 + idx, idx, y);
                     }
                 }

@@ -40,5 +40,33 @@ def main():
         print(f"  {r['Source'].strip()[:70]:70s} inst {r['Instructions Executed']:>10s} wf {r['L1 Wavefronts Shared']:>10s} excess {r['L1 Wavefronts Shared Excessive']:>10s}")
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and not (len(sys.argv) > 2 and sys.argv[2] == "lines"):
     main()
+
+
+def by_line(rep, top=40):
+    """Per CUDA-C source line: warp instructions, stall samples, shared-memory wavefronts (ncu ... --print-source cuda,sass)."""
+    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hi = next(i for i, r in enumerate(rows) if r and r[0] == "Line No")
+    hdr = rows[hi]
+    nm = len(hdr) - 4                                   # metric columns behind (line, source, address, sass)
+    names = hdr[4:]
+    ii, si, wi = names.index("Instructions Executed"), names.index("# Samples"), names.index("L1 Wavefronts Shared")
+    lines = []
+    for r in rows[hi + 1:]:
+        if r and r[0].isdigit() and len(r) >= nm + 2:   # a source line (its text may hold commas: count from the right)
+            m = r[-nm:]
+            try:
+                lines.append((int(r[0]), ",".join(r[1:len(r) - nm]).strip()[:90], int(m[ii] or 0), int(m[si] or 0), int(m[wi] or 0)))
+            except ValueError:
+                pass
+    tot = sum(x[2] for x in lines) or 1
+    tots = sum(x[3] for x in lines) or 1
+    print(f"{'line':>5s} {'warp-inst':>12s} {'%':>6s} {'samples%':>8s} {'smem wf':>11s}  source")
+    for ln, src, inst, smp, wf in sorted(lines, key=lambda x: -x[2])[:top]:
+        print(f"{ln:5d} {inst:12d} {100*inst/tot:6.2f} {100*smp/tots:8.2f} {wf:11d}  {src}")
+
+
+if __name__ == "__main__" and len(sys.argv) > 2 and sys.argv[2] == "lines":
+    by_line(sys.argv[1])
