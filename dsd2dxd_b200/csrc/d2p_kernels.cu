@@ -826,27 +826,35 @@ __device__ __forceinline__ double fir_run(const double* __restrict__ taps, const
 __device__ __forceinline__ double fir_sym_t(const double* __restrict__ taps, const double* __restrict__ col, int h, int D,
                                             int Dp, int sigma, int rf0, int q0) {
     // front element of tap 0 (T0 = 2h-1), shifted: ef = 2h-1+sigma, rf0 = ef mod D, q0 = ef div D (host-computed)
-    int rf = rf0;
+    const int rf = rf0;
     const double* pf = col + q0 * Dp + rf;
     const double* pb = col + sigma;                                 // back element of tap 0: row sigma == D-1-rf, column 0
     const int skip = Dp - D;
     double total = 0.0;
-    int k = 0;
-    while (k < h) {
-        int run = rf + 1;                                           // taps until both walkers leave their columns
-        if (h - k < run) run = h - k;
+    // The first run has (h mod D, or D) = rf0 + 1 taps; with sigma = -h (mod D) every later run is a whole column of D
+    // taps: D = 7, 14 or 28 is walked in sevens, D = 3 in one piece -- no per-run trip-count arithmetic.
+    {
+        const int run = rf + 1;
         int i = 0;
-        for (; i + 7 <= run; i += 7) total = fir_run<7>(taps + k + i, pf, pb, total);   // D is 3, 7, 14 or 28
-        for (; i + 3 <= run; i += 3) total = fir_run<3>(taps + k + i, pf, pb, total);
-        for (; i < run; ++i) total = fir_run<1>(taps + k + i, pf, pb, total);
-        k += run;
-        rf = D - 1; pf -= skip; pb += skip;                         // front: bottom row of the previous column; back: row 0 of the next
+        for (; i + 7 <= run; i += 7) total = fir_run<7>(taps + i, pf, pb, total);
+        for (; i + 3 <= run; i += 3) total = fir_run<3>(taps + i, pf, pb, total);
+        for (; i < run; ++i) total = fir_run<1>(taps + i, pf, pb, total);
+    }
+    if (D == 3) {
+        for (int k = rf + 1; k < h; k += 3) { pf -= skip; pb += skip; total = fir_run<3>(taps + k, pf, pb, total); }
+    } else {
+        for (int k = rf + 1; k < h; k += D) {
+            pf -= skip; pb += skip;                                 // front: bottom row of the previous column; back: row 0 of the next
+            for (int c = 0; c < D; c += 7) total = fir_run<7>(taps + k + c, pf, pb, total);
+        }
     }
     return total;
 }
 
 struct LmTile {                 // per-tile header, computed by one thread
-    const DevJob* J;
+    const DevJob* J;            // the job record: in global memory for the producers; the consumers' copy of the header
+                                // points at `job` below, so the writer's per-sample reads of job fields stay on chip
+    DevJob job;
     long long f0, k2_lo, s_lo;
     int nf, cnt2, j2_0, last_rel, relz, back, dA, nbytes;
     int nch;                    // = P.C; read back from the header so that the channel-group loop keeps its own counter
@@ -932,7 +940,7 @@ __global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __gri
     unsigned int tile = blockIdx.x;
     if (producer && tile < P.total_tiles) {
         lm_tile_header(P, tile, Hc);
-        if (ptid == 0) hdr[0] = Hc;
+        if (ptid == 0) { hdr[0] = Hc; hdr[0].job = *Hc.J; hdr[0].J = &hdr[0].job; }
         stage_input(P, *Hc.J, tiles0, Hc.s_lo, Hc.nbytes, ptid, np);
         cp_async_wait_all();
     }
@@ -945,7 +953,7 @@ __global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __gri
             LmTile Hn; Hn.J = nullptr;
             if (nxt < P.total_tiles) {
                 lm_tile_header(P, nxt, Hn);
-                if (ptid == 0) hdr[bsel ^ 1] = Hn;
+                if (ptid == 0) { hdr[bsel ^ 1] = Hn; hdr[bsel ^ 1].job = *Hn.J; hdr[bsel ^ 1].J = &hdr[bsel ^ 1].job; }
                 stage_input(P, *Hn.J, tiles0 + (size_t)(bsel ^ 1) * tiles_bytes, Hn.s_lo, Hn.nbytes, ptid, np);
             }
             if (Hp.J && staged_out)
