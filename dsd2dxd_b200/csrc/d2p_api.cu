@@ -180,7 +180,8 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
         if (p.gmax > 5 || p.ring_cap != 32 || p.lm_reach() > 31 || (int)p.L > kMaxPhasesDev)   // lm_tile_header's window
             return set_err(D2P_ERR_INVALID_ARG, "internal: stage-1 filter outside the kernel's group / ring assumptions");
         const LmLut ll = lm_lut_layout(p);
-        const int cons = p.nstages == 3 ? kLmConsumers : kLmConsumersSmall;   // see d2p_launch.h
+        int cons = p.nstages == 3 ? kLmConsumers : kLmConsumersSmall;   // see d2p_launch.h
+        if (const char* e = std::getenv("D2P_LM_CONS")) cons = std::atoi(e) > 448 ? kLmConsumers : kLmConsumersSmall;   // tuning knob
         const int nhw = cons / 16;
         { int a = p.m1 % (int)p.L, b = (int)p.L; while (b) { const int t = a % b; a = b; b = t; }
           if (a != 1) return set_err(D2P_ERR_INVALID_ARG, "internal: m1 and L are not coprime"); }
@@ -209,6 +210,7 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
         k.lmA = ll.A; k.lmGp = ll.Gp; k.lm_cyc = ll.cyc; k.lut_row_bytes = ll.slots * 8;
         k.lm_base_hi = p.stage1_nhi(0);
         k.lm_step_t = (long long)p.m1 * ll.A * nhw / p.L;
+        k.lm_step_q = (ll.A * nhw) / p.D2; k.lm_step_ph = (ll.A * nhw) % p.D2;
         k.ostage_bytes = g.ostage;
         dp->threads = cons + kLmProducers;
         k.lm_cons = cons;

@@ -96,6 +96,7 @@ struct KParams {
     int lmA, lmGp, lm_cyc;    // active lanes per half-warp, LUT block pitch (slots, odd), phase patterns (1 or 2)
     long long lm_base_hi;     // high-rate index of stage-1 output 0
     long long lm_step_t;      // input-time step of one half-warp iteration: m1 * A * (threads/16) / L
+    int lm_step_q, lm_step_ph; // the same step in stage-1 outputs, as whole stage-2 periods and the remainder
     unsigned char groups[kMaxPhasesDev];
 
     const uint32_t* fpd_jump; // xorshift32 jump tables: [level 0..3][digit 0..255][byte 0..3][256] (4 MiB), or null

@@ -929,7 +929,7 @@ __global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __gri
     const uint32_t rlo = (uint32_t)P.lut_row_bytes, rhi = (uint32_t)P.lut_row_bytes << 16;
     // one half-warp iteration advances A*nhw outputs: (row, column) step of the phase-major store
     const int step_n = A * nhw;
-    const int step_q = step_n / P.D2, step_ph = step_n - step_q * P.D2;
+    const int step_q = P.lm_step_q, step_ph = P.lm_step_ph;         // step_n div / mod D2 (host-computed)
     const int step_t = (int)P.lm_step_t;                            // = m1 * A * nhw / L (exact)
     const int step_el = step_ph + step_q * P.pitch2, wrap_el = P.pitch2 - P.D2;   // next column: row -= D2
     const int own = A * hw + u;                                     // this thread's output offset from nA
