@@ -243,7 +243,7 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
         for (int K = 1; K <= 16; K <<= 1) {
             if (K > 1 && K - 1 > p.nt) continue;
             const LutLayout L = make_lut_layout(p.nt, K);
-            for (int sl = 1024; sl >= 32; sl >>= 1) {              // slots (frame sets) per channel tile
+            for (int sl = 1024; sl >= 32; sl -= 32) {              // frame sets per channel tile: any multiple of a warp
                 const int tf = setF * sl;
                 int ts, ib, os; size_t sm;
                 lutfir_geometry(p, L, tf, &ts, &ib, &os, &sm);
@@ -253,14 +253,14 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
                 const double busy = spt / std::ceil(spt);                       // idle threads of the last round
                 const double score = (p.nt / steps) * busy * (spt / (spt + 0.12));
                 if (score > best_score) { best_score = score; bestL = L; best_tf = tf; }
-                break;
             }
         }
         if (!best_tf) return set_err(D2P_ERR_NOMEM, "filter LUT and tiles do not fit in shared memory");
         const LutLayout& L = bestL;
         k.TF = best_tf;
         k.setF = setF; k.setDW = setDW;
-        k.sl_shift = 0; while ((setF << k.sl_shift) < best_tf) ++k.sl_shift;
+        k.SL = best_tf / setF;
+        k.sl_inv = (unsigned int)((0x100000000ull + (unsigned)k.SL - 1) / (unsigned)k.SL);
         k.fpw_shift = p.bpo >= 4 ? 0 : (p.bpo == 2 ? 1 : 2);
         lutfir_geometry(p, L, best_tf, &k.tile_stride, &k.in_buf_bytes, &k.ostage_bytes, &dp->smem);
         k.lutK = L.K; k.lut_row_bytes = L.slots * 8;
@@ -292,6 +292,9 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
                           !cfg.keep_f64 && (cfg.dither == 'X' || cfg.dither == 'T' || cfg.dither == 'R') &&
                           sum_abs * std::fabs(p.scale) < 2147483000.0;
     }
+    if (std::getenv("D2P_DEBUG_GEOM"))
+        std::fprintf(stderr, "[d2p] %s: tile %d frames, channel slots in flight %d, K %d, LUT %d B/row x 256, smem %zu B, %d threads\n",
+                     dp->lm ? "lm_kernel" : "lutfir_kernel", k.TF, k.NB, k.lutK, k.lut_row_bytes, dp->smem, dp->threads);
     dp->ctas_per_sm = max_ctas_per_sm(dp->lm, dp->threads, dp->smem);
     if (dp->ctas_per_sm < 1) return set_err(D2P_ERR_CUDA, "kernel cannot be resident with the chosen tile geometry");
     *out = dp.release();

@@ -78,8 +78,10 @@ struct KParams {
     int last_steps;              // steps of the last group that any lane still needs (1..4)
     int zpad_bytes;              // zero region in front of the LUT (idle skew steps read 0.0 from it)
     // frame sets of the integer path: a lane runs setF neighbouring frames (setDW tile words apart) in lockstep;
-    // TF == setF << sl_shift (slots per channel tile), fpw_shift = log2(frames per 32-bit stream word)
-    int setF, setDW, sl_shift, fpw_shift;
+    // TF == setF * SL (SL frame sets per channel tile, a multiple of 32), sl_inv = ceil(2^32 / SL),
+    // fpw_shift = log2(frames per 32-bit stream word)
+    int setF, setDW, SL, fpw_shift;
+    unsigned int sl_inv;
     int nc;                      // consumer threads (the remaining threads of the CTA stage tiles)
     int in_buf_bytes, ostage_bytes;   // per buffer (both are double-buffered)
     // L/M path (A6-A10)

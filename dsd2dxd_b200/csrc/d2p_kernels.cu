@@ -741,10 +741,10 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
             em.set_job(P, *t.J);
             // One item = one frame set: slot s of channel ch holds the frames fl0 + f*fpw, f < F, with
             // fl0 = (s / fpw) * F * fpw + s % fpw  (fpw = frames per 32-bit word of the stream, 1 unless bpo < 4).
-            const int items = P.C << P.sl_shift;
+            const int SL = P.SL, items = P.C * SL;                // SL frame sets per channel (any multiple of 32)
             const int fs = P.fpw_shift, fpw = 1 << fs;
             for (int it = tid; it < items; it += nc) {
-                const int ch = it >> P.sl_shift, slot = it & ((1 << P.sl_shift) - 1);
+                const int ch = (int)__umulhi((unsigned)it, P.sl_inv), slot = it - ch * SL;   // it / SL, it % SL
                 // warp-uniform: the first lane of the warp holds the warp's earliest frame
                 if (((((slot & ~31) >> fs) * F) << fs) >= t.nf) continue;
                 const int fl0 = (((slot >> fs) * F) << fs) + (slot & (fpw - 1));
