@@ -114,3 +114,36 @@ def test_unpinned_state_is_said_out_loud():
     """DESIGN.md must carry the words PARITY UNPINNED exactly as long as no reference-run vectors are committed."""
     design = open(os.path.join(os.path.dirname(HERE), "DESIGN.md")).read()
     assert ("PARITY UNPINNED" in design) == (cases() is None)
+
+
+def test_consumer_accepts_vectors_in_the_dump_layout(ref_files, tmp_path, monkeypatch):
+    """The consumer itself, exercised on vectors in the exact layout tools/ref_dump/make_vectors.py writes -- produced here
+    by the oracle (so this proves the plumbing, not parity): a pass, and a detected one-sample difference."""
+    import sys
+    mod = sys.modules[__name__]
+    out = tmp_path / "reference_vectors"
+    out.mkdir()
+    cases_ = []
+    for rel, fmt, out_rate, bits in (("test/1kHz_mono_p.dsd", dict(channels=1, layout="P", lsb_first=True, dsd_rate=1), 352800, 24),
+                                     ("id3_test/dff/1kHz_stereo_i.dff", dict(container=True), 96000, 32)):
+        case = {"fixture": rel, "format": fmt, "out_rate": out_rate, "filter": "E", "bits": bits, "dither": "X", "returncode": 0}
+        label, pay, kw = payload_variants(ref_files, case)[0]
+        r = orclib.convert(pay, out_rate=out_rate, filt="E", bits=bits, dither="X", **kw)
+        tag = f"case{len(cases_)}"
+        r.pcm.tofile(out / (tag + ".pcm"))
+        r.f64.astype("<f8").tofile(out / (tag + ".f64"))
+        case.update(pcm=tag + ".pcm", f64=tag + ".f64", channels=r.f64.shape[0], frames=r.frames[0])
+        cases_.append(case)
+    json.dump({"cases": cases_}, open(out / "index.json", "w"))
+    monkeypatch.setattr(mod, "VEC", str(out))
+
+    def convert(pay, fmt, case, want_f64):
+        r = orclib.convert(pay, want_f64=want_f64, out_rate=case["out_rate"], filt=case["filter"], bits=case["bits"], dither="X", **fmt)
+        return r.pcm, r.f64, r.frames[0]
+
+    assert [check(c, ref_files, convert) for c in cases()] == ["raw", "dff"]
+    pcm = np.fromfile(out / "case0.pcm", dtype=np.uint8)
+    pcm[1000] ^= 1
+    pcm.tofile(out / "case0.pcm")
+    with pytest.raises(AssertionError, match="differs from the reference"):
+        check(cases()[0], ref_files, convert)
