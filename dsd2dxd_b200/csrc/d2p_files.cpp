@@ -223,7 +223,7 @@ bool build_header(int container, int bits, int channels, uint32_t rate, uint64_t
     }
 }
 
-struct FileCloser { FILE* f; ~FileCloser() { if (f) std::fclose(f); } };
+struct FileCloser { FILE* f; void close() { if (f) std::fclose(f); f = nullptr; } ~FileCloser() { close(); } };
 
 }  // namespace
 
@@ -376,48 +376,32 @@ int d2p_convert_file_ex(const d2p_file_options* opt, const char* in_path, const 
     int st = d2p_plan(&cfg, &pi);
     if (st != D2P_OK) return st;
 
+    // What the reader hands over: whole block groups read linearly from the file, then (DSF stopped at fmt.sample_count)
+    // a ragged last group in which every channel's run is `tail` bytes long and the runs follow each other -- the layout
+    // both conversion paths expect for a partial group.
     const uint64_t per_ch = ci.data_bytes / ci.channels;
-    const uint64_t frames_max = d2p_frames_for_bytes(&cfg, per_ch);
-    const size_t out_cap = (size_t)frames_max * ci.channels * pi.bytes_per_sample;
-    uint8_t* h_in = (uint8_t*)d2p_host_alloc(std::max<size_t>((size_t)ci.data_bytes, 16));
-    uint8_t* h_out = (uint8_t*)d2p_host_alloc(std::max<size_t>(out_cap, 16));
-    struct Free { uint8_t* a; uint8_t* b; ~Free() { d2p_host_free(a); d2p_host_free(b); } } fr{h_in, h_out};
-    if (!h_in || !h_out) return api_set_error(D2P_ERR_NOMEM, "pinned host allocation failed");
-    if (std::fseek(fc.f, (long)ci.data_offset, SEEK_SET) != 0 ||
-        std::fread(h_in, 1, (size_t)ci.data_bytes, fc.f) != (size_t)ci.data_bytes)
-        return api_set_error(D2P_ERR_INVALID_ARG, "short read of the DSD payload");
-
-    size_t in_bytes = (size_t)ci.data_bytes;
+    uint64_t linear_bytes = ci.data_bytes, tail = 0, per_ch_used = per_ch;
+    const size_t group = (size_t)ci.channels * ci.block_size;
     if (ci.format == D2P_CONTAINER_DSF && opt->dsf_stop_at_sample_count) {
-        // stop at fmt.sample_count: whole block groups, then a ragged last group in which every channel's run is
-        // tail bytes long and the runs follow each other (the layout d2p_convert_host expects for a partial group)
-        const uint64_t limit = std::min<uint64_t>((ci.sample_count + 7) / 8, per_ch);
-        const uint64_t full = limit / ci.block_size, tail = limit % ci.block_size;
-        const size_t group = (size_t)ci.channels * ci.block_size;
-        if (tail)
-            for (int c = 0; c < ci.channels; ++c)
-                std::memmove(h_in + full * group + (size_t)c * tail, h_in + full * group + (size_t)c * ci.block_size, (size_t)tail);
-        in_bytes = (size_t)(full * group + tail * ci.channels);
+        per_ch_used = std::min<uint64_t>((ci.sample_count + 7) / 8, per_ch);
+        linear_bytes = per_ch_used / ci.block_size * group;
+        tail = per_ch_used % ci.block_size;
     }
-    uint64_t frames = 0;
-    {
-        d2p_batch* b = nullptr;
-        st = d2p_batch_create(&cfg, &b);
-        if (st != D2P_OK) return st;
-        d2p_batch_set_control(b, cancel_flag, progress, user);
-        st = d2p_batch_convert_host(b, h_in, in_bytes, h_out, out_cap, &frames);
-        if (st == D2P_OK) st = d2p_batch_stats(b, nullptr, &R.clipped_samples, &R.peak_abs);
-        d2p_batch_destroy(b);
-        if (st != D2P_OK) return st;                               // nothing has been written yet
-    }
-    R.frames = frames;
+    const uint64_t frames_max = d2p_frames_for_bytes(&cfg, per_ch_used);
+    auto read_tail = [&](uint8_t* dst) -> bool {                   // the ragged group, compacted: [ch0 tail | ch1 tail | ...]
+        std::vector<uint8_t> g(group);
+        if (std::fseek(fc.f, (long)(ci.data_offset + linear_bytes), SEEK_SET) != 0 || std::fread(g.data(), 1, group, fc.f) != group) return false;
+        for (int c = 0; c < ci.channels; ++c) std::memcpy(dst + (size_t)c * tail, g.data() + (size_t)c * ci.block_size, (size_t)tail);
+        return true;
+    };
+
     // ---- metadata carry-over (save_output, rd/conversion_context.rs:565-590) ----
     std::vector<uint8_t> id3;
     if (opt->copy_tags && ci.id3_offset && ci.id3_bytes >= 10 && ci.id3_bytes < (64u << 20)) {
         id3.resize((size_t)ci.id3_bytes);
         if (std::fseek(fc.f, (long)ci.id3_offset, SEEK_SET) != 0 || std::fread(id3.data(), 1, id3.size(), fc.f) != id3.size() ||
             !tag_usable(id3.data(), id3.size()))
-            id3.clear();                                           // "Input file has no id3; skipping id3 copy."
+            id3.clear();                                           // "Input file has no tag; skipping tag copy."
     }
     if (!id3.empty() && opt->append_rate) {
         const char* dot = nullptr;                                 // abbrev_rate_pair :603-621
@@ -428,24 +412,95 @@ int d2p_convert_file_ex(const d2p_file_options* opt, const char* in_path, const 
         }
         if (dot) tag_append_album(&id3, dot);
     }
-    if (opt->out_container == D2P_FILE_FLAC && !id3.empty()) {
+    auto fail = [&](int code) {                                    // no partly written file is left behind
+        if (std::strncmp(out_path, "/dev/", 5) != 0) std::remove(out_path);
+        return code;
+    };
+
+    uint64_t frames = 0;
+    if (opt->out_container == D2P_FILE_FLAC) {
+        // The FLAC encoder wants the whole stream (STREAMINFO totals, MD5): payload and PCM are held in pinned memory and
+        // go through the pipelined whole-payload conversion.
+        const size_t out_cap = (size_t)frames_max * ci.channels * pi.bytes_per_sample;
+        const size_t in_bytes = (size_t)(linear_bytes + tail * ci.channels);
+        uint8_t* h_in = (uint8_t*)d2p_host_alloc(std::max<size_t>(in_bytes, 16));
+        uint8_t* h_out = (uint8_t*)d2p_host_alloc(std::max<size_t>(out_cap, 16));
+        struct Free { uint8_t* a; uint8_t* b; ~Free() { d2p_host_free(a); d2p_host_free(b); } } fr{h_in, h_out};
+        if (!h_in || !h_out) return api_set_error(D2P_ERR_NOMEM, "pinned host allocation failed");
+        if (std::fseek(fc.f, (long)ci.data_offset, SEEK_SET) != 0 || std::fread(h_in, 1, (size_t)linear_bytes, fc.f) != (size_t)linear_bytes ||
+            (tail && !read_tail(h_in + linear_bytes)))
+            return api_set_error(D2P_ERR_INVALID_ARG, "short read of the DSD payload");
+        d2p_batch* b = nullptr;
+        st = d2p_batch_create(&cfg, &b);
+        if (st != D2P_OK) return st;
+        d2p_batch_set_control(b, cancel_flag, progress, user);
+        st = d2p_batch_convert_host(b, h_in, in_bytes, h_out, out_cap, &frames);
+        if (st == D2P_OK) st = d2p_batch_stats(b, nullptr, &R.clipped_samples, &R.peak_abs);
+        d2p_batch_destroy(b);
+        if (st != D2P_OK) return st;                               // nothing has been written yet
         std::vector<std::string> comments, strings;
         std::vector<d2p_flac_picture> pics;
         std::vector<std::vector<uint8_t>> storage;
-        tag_to_flac(id3.data(), id3.size(), &comments, &pics, &storage, &strings);
+        if (!id3.empty()) tag_to_flac(id3.data(), id3.size(), &comments, &pics, &storage, &strings);
         std::vector<const char*> cptr;
         for (const std::string& c : comments) cptr.push_back(c.c_str());
         st = d2p_write_flac_file_ex(out_path, opt->bits, ci.channels, opt->out_rate, h_out, frames, cptr.data(), (int)cptr.size(),
                                     pics.data(), (int)pics.size());
+        if (st != D2P_OK) return fail(st);
     } else {
-        st = d2p_write_pcm_file(out_path, opt->out_container, opt->bits, ci.channels, opt->out_rate, h_out, frames);
-        if (st == D2P_OK && !id3.empty() && opt->out_container != D2P_FILE_RAW && opt->out_container != D2P_FILE_FLAC)
-            st = append_id3_chunk(out_path, opt->out_container == D2P_FILE_WAV, id3);
+        // WAV / AIFF / AIFC / headerless: the file is streamed through the GPU in 64 MiB slices with bounded pinned memory
+        // (two buffers, whatever the length of the input: a 60-minute 6-channel DSD512 payload is 61 GB).  The streaming
+        // context keeps the filter halo between slices, so the bytes equal the one-pass conversion.
+        Bytes h;
+        if (opt->out_container != D2P_FILE_RAW && !build_header(opt->out_container, opt->bits, ci.channels, opt->out_rate, frames_max, &h))
+            return api_set_error(D2P_ERR_BIT_DEPTH, "Unsupported bit depth");
+        const size_t slice = std::max<size_t>(group, ((size_t)64 << 20) / group * group);
+        const size_t fb = (size_t)ci.channels * pi.bytes_per_sample, out_cap = ((size_t)48 << 20) / fb * fb + fb;
+        uint8_t* h_in = (uint8_t*)d2p_host_alloc(std::max<size_t>(std::min<uint64_t>(slice, std::max<uint64_t>(linear_bytes, group)), 16));
+        uint8_t* h_out = (uint8_t*)d2p_host_alloc(out_cap);
+        struct Free { uint8_t* a; uint8_t* b; ~Free() { d2p_host_free(a); d2p_host_free(b); } } fr{h_in, h_out};
+        if (!h_in || !h_out) return api_set_error(D2P_ERR_NOMEM, "pinned host allocation failed");
+        d2p_ctx* ctx = nullptr;
+        st = d2p_create(&cfg, &ctx);
+        if (st != D2P_OK) return st;
+        struct Ctx { d2p_ctx* c; ~Ctx() { d2p_destroy(c); } } guard{ctx};
+        FileCloser of{std::fopen(out_path, "wb")};
+        if (!of.f) return api_set_error(D2P_ERR_INVALID_ARG, (std::string("cannot create ") + out_path).c_str());
+        if (!h.v.empty() && std::fwrite(h.v.data(), 1, h.v.size(), of.f) != h.v.size()) return fail(api_set_error(D2P_ERR_INVALID_ARG, "write failed"));
+        auto drain = [&]() -> int {
+            for (;;) {
+                uint64_t n = 0;
+                const int s2 = d2p_pull(ctx, h_out, out_cap, &n);
+                if (s2 != D2P_OK) return s2;
+                if (n == 0) return D2P_OK;
+                if (std::fwrite(h_out, fb, (size_t)n, of.f) != (size_t)n) return api_set_error(D2P_ERR_INVALID_ARG, "write failed");
+                frames += n;
+                if (progress) progress(user, frames, frames_max);
+            }
+        };
+        if (std::fseek(fc.f, (long)ci.data_offset, SEEK_SET) != 0) return fail(api_set_error(D2P_ERR_INVALID_ARG, "short read of the DSD payload"));
+        for (uint64_t done = 0; done < linear_bytes;) {
+            if (cancel_flag && *cancel_flag) return fail(api_set_error(D2P_ERR_CANCELLED, "conversion cancelled"));
+            const size_t n = (size_t)std::min<uint64_t>(slice, linear_bytes - done);
+            if (std::fread(h_in, 1, n, fc.f) != n) return fail(api_set_error(D2P_ERR_INVALID_ARG, "short read of the DSD payload"));
+            if ((st = d2p_push(ctx, h_in, n)) != D2P_OK || (st = drain()) != D2P_OK) return fail(st);
+            done += n;
+        }
+        if (cancel_flag && *cancel_flag) return fail(api_set_error(D2P_ERR_CANCELLED, "conversion cancelled"));
+        if (tail) {
+            if (!read_tail(h_in)) return fail(api_set_error(D2P_ERR_INVALID_ARG, "short read of the DSD payload"));
+            if ((st = d2p_push(ctx, h_in, (size_t)(tail * ci.channels))) != D2P_OK) return fail(st);
+        }
+        if ((st = d2p_finish(ctx)) != D2P_OK || (st = drain()) != D2P_OK) return fail(st);
+        if (frames != frames_max) return fail(api_set_error(D2P_ERR_STATE, "internal: frame count differs from the plan"));
+        int64_t clips = 0;
+        if ((st = d2p_stats(ctx, &clips, &R.peak_abs, &R.clipped_samples)) != D2P_OK) return fail(st);
+        if (std::fflush(of.f) != 0) return fail(api_set_error(D2P_ERR_INVALID_ARG, "write failed"));
+        of.close();
+        if (!id3.empty() && opt->out_container != D2P_FILE_RAW && (st = append_id3_chunk(out_path, opt->out_container == D2P_FILE_WAV, id3)) != D2P_OK)
+            return fail(st);
     }
-    if (st != D2P_OK) {                                            // no partly written file is left behind
-        if (std::strncmp(out_path, "/dev/", 5) != 0) std::remove(out_path);
-        return st;
-    }
+    R.frames = frames;
     R.tag_bytes = id3.size();
     if (opt->out_container == D2P_FILE_FLAC) {                     // compressed: the size is whatever the encoder produced
         FileCloser of{std::fopen(out_path, "rb")};

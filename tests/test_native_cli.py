@@ -183,3 +183,22 @@ def test_convert_file_draws_a_seed_when_none_is_given(ref_files, tmp_path):
     assert (tmp_path / "c.wav").read_bytes() == (tmp_path / "a.wav").read_bytes()          # reproducible from the report
     x = d2p.convert_file(src, tmp_path / "x.wav", out_rate=176400, bits=16, dither="X")
     assert x["dither_seed"] == 0
+
+
+@pytest.mark.gpu
+def test_convert_file_streams_long_files_in_bounded_slices(tmp_path):
+    """A payload of several 64 MiB slices plus a ragged end goes through the streaming context with two fixed pinned
+    buffers (the whole-payload staging needed 7 GB for a 60-minute multichannel file): the bytes equal the
+    oracle's one-pass conversion and the progress callback walks up to the total."""
+    per_ch = 4096 * 22000 + 1234                                   # 3 slices of 64 MiB and a partial block group
+    raw = np.random.default_rng(9).integers(0, 256, size=2 * per_ch, dtype=np.uint8)
+    src = tmp_path / "long.dsd"
+    raw.tofile(src)
+    seen = []
+    res = d2p.convert_file(src, tmp_path / "o.wav", out_rate=176400, bits=24, container="W", raw_channels=2, raw_layout="P",
+                           raw_lsb_first=True, raw_dsd_rate=4, progress=lambda done, total: seen.append((done, total)))
+    ref = orclib.convert(raw, dsd_rate=4, out_rate=176400, bits=24, channels=2, stdout_mode=False, want_f64=False)
+    assert res["frames"] == ref.frames[0]
+    assert (tmp_path / "o.wav").read_bytes() == orc.WRITERS["W"](ref.planar, 24, 176400)
+    assert len(seen) >= 3 and seen[-1] == (ref.frames[0], ref.frames[0]) and all(a[0] < b[0] for a, b in zip(seen, seen[1:]))
+    assert res["peak_abs"] == np.abs(orclib.convert(raw, dsd_rate=4, out_rate=176400, bits=24, channels=2).f64 * (1 << 23)).max()
