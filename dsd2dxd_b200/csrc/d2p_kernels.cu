@@ -339,10 +339,11 @@ struct Emitter {
 
     // WM == 1 in two halves, so that a caller can run the pure arithmetic of several samples side by side:
     // quant = scale, level, dither, round (no memory access, no branch); put = clamp, clip statistics, pack.
-    __device__ __forceinline__ int quant(const KParams& P, int ch, long long f, double y) {
+    // live: the frame exists (lanes past the end of a ragged tile compute along but must not reach the statistics)
+    __device__ __forceinline__ int quant(const KParams& P, int ch, long long f, double y, bool live) {
         double s = __dmul_rn(y, P.scale);                       // scale_and_dither  rd/pcm_writer.rs:651
         const unsigned long long ab = (unsigned long long)__double_as_longlong(fabs(s));
-        peakb = ab > peakb ? ab : peakb;                        // process_levels    rd/conversion_context.rs:235-240
+        peakb = (live && ab > peakb) ? ab : peakb;              // process_levels    rd/conversion_context.rs:235-240
         if (DITH) s = __dadd_rn(s, dither_noise(DITH, (unsigned long long)f, (uint32_t)ch, key));
         // quantize / my_round   rd/pcm_writer.rs:678-705 ; floor fused into the conversion
         return __double2int_rd(__dadd_rn(s, s < 0.0 ? -0.5 : 0.5));
@@ -359,7 +360,7 @@ struct Emitter {
     // y: decimator output of channel ch, absolute frame f; fl: frame index inside the tile
     __device__ __forceinline__ void emit(const KParams& P, const DevJob& J, unsigned char* ostage,
                                          int ch, long long f, int fl, double y) {
-        if (WM == 1) { put(P, J, ostage, ch, f, fl, quant(P, ch, f, y)); return; }
+        if (WM == 1) { put(P, J, ostage, ch, f, fl, quant(P, ch, f, y, true)); return; }
         const long long fj = f - J.f_begin;
         if (J.f64) J.f64[(long long)ch * J.f64_stride + fj] = y;
         double s = __dmul_rn(y, P.scale);                       // scale_and_dither  rd/pcm_writer.rs:651
@@ -754,7 +755,7 @@ __global__ void __launch_bounds__(kLutfirThreads, 1) lutfir_kernel(const __grid_
                 if (WM == 1) {                                  // the dither / rounding chains of the set side by side
                     int v[F];
 #pragma unroll
-                    for (int f = 0; f < F; ++f) v[f] = em.quant(P, ch, t.f0 + fl0 + (f << fs), y[f]);
+                    for (int f = 0; f < F; ++f) v[f] = em.quant(P, ch, t.f0 + fl0 + (f << fs), y[f], fl0 + (f << fs) < t.nf);
 #pragma unroll
                     for (int f = 0; f < F; ++f) {
                         const int fl = fl0 + (f << fs);

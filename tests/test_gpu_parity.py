@@ -413,3 +413,21 @@ def test_randomised_configurations_match_oracle():
         assert np.array_equal(np.concatenate(got), ref.pcm), kw
         done += 1
     assert done >= 40
+
+
+@pytest.mark.parametrize("dither", ["X", "T"])
+def test_fast_writer_statistics_ignore_lanes_past_a_ragged_tile(dither):
+    """The specialised 3-byte writer runs whole frame sets; frames past the end of the last (ragged) tile are computed
+    along but must reach neither the PCM nor the peak / clip statistics."""
+    raw = rand_payload(4321, 2, 301)[: 2 * (4096 * 300 + 1234)]
+    kw = dict(dsd_rate=4, out_rate=176400, bits=24, channels=2, dither=dither, dither_seed=3)
+    cfg = d2p.make_config(**kw)
+    conv = d2p.Converter(cfg)                                    # no f64 side output: Emitter<1, .>
+    conv.push(raw)
+    conv.finish()
+    pcm = conv.pull()
+    st = conv.stats()
+    conv.close()
+    ref = orclib.convert(raw, **kw)
+    assert np.array_equal(pcm, ref.pcm)
+    assert st["peak_abs"] == np.abs(ref.f64 * ref.scale).max() and st["clipped_samples"] == 0 and st["clips"] == ref.clips
