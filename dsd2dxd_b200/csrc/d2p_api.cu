@@ -180,28 +180,45 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
         if (p.gmax > 5 || p.ring_cap != 32 || p.lm_reach() > 31 || (int)p.L > kMaxPhasesDev)   // lm_tile_header's window
             return set_err(D2P_ERR_INVALID_ARG, "internal: stage-1 filter outside the kernel's group / ring assumptions");
         const LmLut ll = lm_lut_layout(p);
-        int cons = p.nstages == 3 ? kLmConsumers : kLmConsumersSmall;   // see d2p_launch.h
-        if (const char* e = std::getenv("D2P_LM_CONS")) cons = std::atoi(e) > 448 ? kLmConsumers : kLmConsumersSmall;   // tuning knob
-        const int nhw = cons / 16;
         { int a = p.m1 % (int)p.L, b = (int)p.L; while (b) { const int t = a % b; a = b; b = t; }
           if (a != 1) return set_err(D2P_ERR_INVALID_ARG, "internal: m1 and L are not coprime"); }
-        if (((long long)p.m1 * ll.A * nhw) % p.L != 0 || (ll.cyc == 2 && ((long long)p.m1 * ll.A * 2) % p.L != 0))
-            return set_err(D2P_ERR_INVALID_ARG, "internal: stage-1 phase pattern does not close");
-        // tile geometry: keep the whole CTA busy in stages 2/3 (NB * TF >= threads) with the largest tile that fits
-        int best_tf = 0, best_nb = 0; double best_score = 0.0;
+        // Tile geometry per build (448 / 896 consumers, d2p_launch.h): keep the whole CTA busy in stages 2/3 (NB * TF a
+        // multiple of the consumer count) with the largest tile that fits.
         const int C = cfg.channels;
         const double halo = p.nstages == 3 ? (2.0 * p.h3 / p.D3 + 2.0 * p.h2 / (p.D2 * p.D3)) : 2.0 * p.h2 / p.D2;
-        for (int tf = 1024; tf >= 32; tf -= 32)
-            for (int nb = 1; nb <= C; ++nb) {
-                if (C % nb != 0 && nb != C) continue;
-                const LmGeom g = lm_geometry(p, ll, tf, nb);
-                if (g.smem > budget) continue;
-                // stages 2/3 hand one output to each consumer thread per round: count the idle threads of the last round
-                const double items = (double)nb * tf;
-                const double busy = items / (std::ceil(items / cons) * cons);
-                const double score = busy * tf / (tf + halo);
-                if (score > best_score * 1.0001) { best_score = score; best_tf = tf; best_nb = nb; }
-            }
+        struct Pick { int cons, tf, nb; double score; };
+        auto pick = [&](int cons_) {
+            Pick b{cons_, 0, 0, 0.0};
+            const int nhw_ = cons_ / 16;
+            if (((long long)p.m1 * ll.A * nhw_) % p.L != 0 || (ll.cyc == 2 && ((long long)p.m1 * ll.A * 2) % p.L != 0)) return b;
+            for (int tf = 1024; tf >= 32; tf -= 32)
+                for (int nb = 1; nb <= C; ++nb) {
+                    if (C % nb != 0 && nb != C) continue;
+                    const LmGeom g = lm_geometry(p, ll, tf, nb);
+                    if (g.smem > budget) continue;
+                    // stages 2/3 hand one output to each consumer thread per round: count the idle threads of the last round
+                    const double items = (double)nb * tf;
+                    const double busy = items / (std::ceil(items / cons_) * cons_);
+                    const double score = busy * tf / (tf + halo);
+                    if (score > b.score * 1.0001) { b.score = score; b.tf = tf; b.nb = nb; }
+                }
+            return b;
+        };
+        const Pick small = pick(kLmConsumersSmall), large = pick(kLmConsumers);
+        // Which build (measured over all twelve topologies, tools/lm_cons_sweep.sh): the three-stage chains and the short
+        // two-stage filters (stage 2 decimating by 7) run best on 896 consumers (64 registers) -- the latter only while
+        // their tiles keep that many threads busy (6-channel input does not) -- the long two-stage filters walked in whole
+        // columns of 14 or 28 taps (DSD256 -> 96 / 192 kHz) want the 128 registers of the 448-consumer build.
+        Pick best = small;
+        if (p.nstages == 3) best = large;
+        else if (p.D2 < 14 && large.tf && large.score >= 0.9 * small.score) best = large;
+        if (!best.tf) best = small.tf ? small : large;
+        if (const char* e = std::getenv("D2P_LM_CONS")) {                  // tuning knob
+            const Pick forced = std::atoi(e) > 448 ? large : small;
+            if (forced.tf) best = forced;
+        }
+        const int cons = best.cons, nhw = cons / 16;
+        const int best_tf = best.tf, best_nb = best.nb;
         if (!best_tf) return set_err(D2P_ERR_NOMEM, "filter LUT and tiles do not fit in shared memory");
         const LmGeom g = lm_geometry(p, ll, best_tf, best_nb);
         k.TF = best_tf; k.NB = best_nb;
