@@ -8,8 +8,8 @@
 //                   + direct symmetric FIR stages 2/3 (DecimFIRSym, :645-752) chained through shared
 //                   memory per output tile, same fused writer epilogue.
 //
-// Both are persistent kernels: each CTA copies the filter's LUT into shared memory once and then walks
-// tiles of output frames.  A tile is computed from absolute input positions (halo included), so tiles,
+// Both are persistent kernels (one CTA per SM): each CTA copies the filter's LUT into shared memory once and then
+// walks tiles of output frames.  A tile is computed from absolute input positions (halo included), so tiles,
 // files and time blocks are independent -- no state is carried between them.
 //
 // Bit-exactness: every f64 operation is an explicit __dadd_rn/__dmul_rn in the reference's order
@@ -474,14 +474,16 @@ __device__ __forceinline__ void load_lut(double* dst, const double* __restrict__
 //   * lane (r, c) of a half-warp (R = 16/K replicas x K skews) runs table i at step u = i + c, so at any
 //     step the 16 lanes address 16 different bank pairs: every look-up costs exactly 2 wavefronts;
 //   * the fold order per frame is untouched (each lane still walks i = 0..nt-1), so results stay
-//     bit-exact; the price is K-1 idle steps per frame (guarded: the DADDs are predicated off).
+//     bit-exact; the price is K-1 idle steps per frame set, which read 0.0 from a zero region in front of the LUT at
+//     the bank pair the live look-up would have used (acc + 0.0 == acc exactly, no predicated arithmetic).
 // Input bytes are fetched as aligned 32-bit words and funnel-shifted into 4-byte groups; the mirrored half
 // is bit-reversed 4 bytes at a time with one BREV (which also flips the byte order, so both halves are
 // consumed from the top byte down).
 //
 // The CTA is warp-specialised: P.nc consumer threads only touch shared memory (LUT, input tile, output
-// staging), the remaining threads stage the next input tile from HBM and copy the previous tile's
-// packed PCM out, over double-buffered tiles -- one __syncthreads per tile.
+// staging); the remaining threads stage the next input tile -- TMA bulk copies completed on an mbarrier for the
+// untransformed interior of DSF-style payloads, register transposes for MSB-first / byte-interleaved sources -- and
+// write the previous tile's packed PCM out with one bulk store, over double-buffered tiles: one __syncthreads per tile.
 // ------------------------------------------------------------------------------------------------
 struct TileInfo {
     const DevJob* J;
