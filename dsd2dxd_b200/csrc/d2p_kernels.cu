@@ -900,6 +900,40 @@ __device__ __forceinline__ void lm_tile_header(const KParams& P, unsigned int ti
     H.dA = (int)(tA - 31 - 8 * s_lo);                              // tile-relative bit of output nA's oldest window bit
 }
 
+// N consecutive stage-1 outputs of one lane (input-time step dt bits, store step sq doubles): y = fold_g LUT[p][g][window
+// byte g] (Stage1Poly, rd/lm_resampler.rs:603-640), the windows' bit j = x[t - j]; group 4 re-reads byte 0 (8g mod 32).
+template <int GMAX, int N>
+__device__ __forceinline__ void stage1_outputs(const uint32_t* __restrict__ tw, int d, int dt, uint32_t rlo, uint32_t rhi,
+                                               uint32_t tpl, double* pd, int sq) {
+    uint32_t z[N];
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+        const int dk = d + k * dt, w = dk >> 5;
+        z[k] = __brev(__funnelshift_r(tw[w], tw[w + 1], dk & 31));
+    }
+    double y[N];
+#pragma unroll
+    for (int k = 0; k < N; ++k) y[k] = lds_f64<0>(__dp2a_lo(rlo, z[k], tpl));
+    if (GMAX > 1) {
+#pragma unroll
+        for (int k = 0; k < N; ++k) y[k] = __dadd_rn(y[k], lds_f64<8>(__dp2a_lo(rhi, z[k], tpl)));
+    }
+    if (GMAX > 2) {
+#pragma unroll
+        for (int k = 0; k < N; ++k) y[k] = __dadd_rn(y[k], lds_f64<16>(__dp2a_hi(rlo, z[k], tpl)));
+    }
+    if (GMAX > 3) {
+#pragma unroll
+        for (int k = 0; k < N; ++k) y[k] = __dadd_rn(y[k], lds_f64<24>(__dp2a_hi(rhi, z[k], tpl)));
+    }
+    if (GMAX > 4) {
+#pragma unroll
+        for (int k = 0; k < N; ++k) y[k] = __dadd_rn(y[k], lds_f64<32>(__dp2a_lo(rlo, z[k], tpl)));
+    }
+#pragma unroll
+    for (int k = 0; k < N; ++k) pd[k * sq] = y[k];
+}
+
 template <int NCONS>
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" :: "n"(NCONS) : "memory"); }
 
@@ -993,30 +1027,13 @@ __global__ void __launch_bounds__(NCONS + kLmProducers, 1) lm_kernel(const __gri
                         if (step_ph == 0 && relz <= rel0) {
                             // the usual case: a round advances a whole number of stage-2 periods (the lane's row of the
                             // phase-major tile never changes) and every output of the tile exists
-                            // two outputs per round trip: both windows are fetched and all ten look-ups issued before the
+                            // several outputs per round trip: all windows are fetched and all look-ups issued before the
                             // first store (stores to the stage-1 tile may alias the input tile as far as the compiler knows)
                             int rel = rel0, d = d0;
-                            for (; rel + step_n <= last_rel; rel += 2 * step_n, d += 2 * step_t, pd += 2 * sq) {
-                                const int w0 = d >> 5, d1 = d + step_t, w1 = d1 >> 5;
-                                const uint32_t z0 = __brev(__funnelshift_r(tw[w0], tw[w0 + 1], d & 31));   // bit j = x[t-j]
-                                const uint32_t z1 = __brev(__funnelshift_r(tw[w1], tw[w1 + 1], d1 & 31));
-                                double y0 = lds_f64<0>(__dp2a_lo(rlo, z0, tpl)), y1 = lds_f64<0>(__dp2a_lo(rlo, z1, tpl));
-                                if (GMAX > 1) { y0 = __dadd_rn(y0, lds_f64<8>(__dp2a_lo(rhi, z0, tpl))); y1 = __dadd_rn(y1, lds_f64<8>(__dp2a_lo(rhi, z1, tpl))); }
-                                if (GMAX > 2) { y0 = __dadd_rn(y0, lds_f64<16>(__dp2a_hi(rlo, z0, tpl))); y1 = __dadd_rn(y1, lds_f64<16>(__dp2a_hi(rlo, z1, tpl))); }
-                                if (GMAX > 3) { y0 = __dadd_rn(y0, lds_f64<24>(__dp2a_hi(rhi, z0, tpl))); y1 = __dadd_rn(y1, lds_f64<24>(__dp2a_hi(rhi, z1, tpl))); }
-                                if (GMAX > 4) { y0 = __dadd_rn(y0, lds_f64<32>(__dp2a_lo(rlo, z0, tpl))); y1 = __dadd_rn(y1, lds_f64<32>(__dp2a_lo(rlo, z1, tpl))); }
-                                pd[0] = y0; pd[sq] = y1;
-                            }
-                            if (rel <= last_rel) {
-                                const int w = d >> 5;
-                                const uint32_t z = __brev(__funnelshift_r(tw[w], tw[w + 1], d & 31));
-                                double y = lds_f64<0>(__dp2a_lo(rlo, z, tpl));
-                                if (GMAX > 1) y = __dadd_rn(y, lds_f64<8>(__dp2a_lo(rhi, z, tpl)));
-                                if (GMAX > 2) y = __dadd_rn(y, lds_f64<16>(__dp2a_hi(rlo, z, tpl)));
-                                if (GMAX > 3) y = __dadd_rn(y, lds_f64<24>(__dp2a_hi(rhi, z, tpl)));
-                                if (GMAX > 4) y = __dadd_rn(y, lds_f64<32>(__dp2a_lo(rlo, z, tpl)));   // 8g mod 32: byte 0 again
-                                *pd = y;
-                            }
+                            // (two at a time: four in flight measured the same -- stage 1 does not wait on its own loads)
+                            for (; rel + step_n <= last_rel; rel += 2 * step_n, d += 2 * step_t, pd += 2 * sq)
+                                stage1_outputs<GMAX, 2>(tw, d, step_t, rlo, rhi, tpl, pd, sq);
+                            if (rel <= last_rel) stage1_outputs<GMAX, 1>(tw, d, step_t, rlo, rhi, tpl, pd, sq);
                             continue;
                         }
                         int ph = p0, d = d0;
