@@ -135,7 +135,10 @@ int  d2p_pull(d2p_ctx* ctx, void* pcm, size_t cap_bytes, uint64_t* frames);
  * oldest frame not yet pulled by d2p_pull.  Does not consume. */
 int  d2p_pull_f64(d2p_ctx* ctx, int chan, double* out, size_t cap, uint64_t* n);
 /* clips: PcmWriter::clips semantics (rd/pcm_writer.rs:658-675); peak_abs: max |sample*scale|
- * (process_levels, rd/conversion_context.rs:209-256); clipped_samples: plain count. */
+ * (process_levels, rd/conversion_context.rs:209-256); clipped_samples: plain count.
+ * `clips` replays the reference's run-length counter in its processing order (block, channel, frame), which is only
+ * settled for whole reader blocks: call it after d2p_finish (before that, clip events of the unfinished last block may
+ * still be ordered differently from the final stream; peak_abs and clipped_samples are exact at any time). */
 int  d2p_stats(d2p_ctx* ctx, int64_t* clips, double* peak_abs, int64_t* clipped_samples);
 
 /* ---- whole-payload conversion with host buffers (pipelined H2D / kernel / D2H) ------------------- */
