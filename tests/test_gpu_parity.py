@@ -431,3 +431,30 @@ def test_fast_writer_statistics_ignore_lanes_past_a_ragged_tile(dither):
     ref = orclib.convert(raw, **kw)
     assert np.array_equal(pcm, ref.pcm)
     assert st["peak_abs"] == np.abs(ref.f64 * ref.scale).max() and st["clipped_samples"] == 0 and st["clips"] == ref.clips
+
+
+@pytest.mark.parametrize("in_off,out_off", [(0, 0), (1, 0), (0, 2), (7, 9), (16, 16)])
+@pytest.mark.parametrize("kw", [dict(dsd_rate=4, out_rate=352800, bits=24, channels=2, dither="T"),
+                                dict(dsd_rate=1, out_rate=96000, bits=16, channels=2)])
+def test_unaligned_device_buffers_take_the_register_paths(in_off, out_off, kw):
+    """TMA bulk copies need 16-byte aligned addresses on both sides: a payload or an output buffer that is not aligned
+    must fall back to the per-thread loads / stores (per job, inside the same launch as aligned jobs) and give the same bytes."""
+    torch = pytest.importorskip("torch")
+    raws = [rand_payload(700 + i, 2, 40 + 3 * i) for i in range(3)]
+    cfg = d2p.make_config(dither_seed=5, **kw)
+    bps = d2p.plan(cfg)["bytes_per_sample"]
+    batch = d2p.Batch(cfg)
+    offs = [(in_off, out_off), (0, 0), (in_off, 0)]                  # aligned and unaligned jobs side by side
+    d_in = [torch.zeros(r.size + 32, dtype=torch.uint8, device="cuda") for r in raws]
+    for t, r, (a, _) in zip(d_in, raws, offs):
+        t[a:a + r.size] = torch.from_numpy(r).cuda()
+    nbytes = [d2p.total_frames(cfg, r.size) * 2 * bps for r in raws]
+    d_out = [torch.zeros(n + 64, dtype=torch.uint8, device="cuda") for n in nbytes]
+    jobs = batch.make_jobs(dict(d_in=t.data_ptr() + a, in_bytes=r.size, d_out=o.data_ptr() + b, out_cap_bytes=n + 16, dither_seed=5)
+                           for t, r, o, n, (a, b) in zip(d_in, raws, d_out, nbytes, offs))
+    batch.run(jobs, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    for r, o, n, (_, b) in zip(raws, d_out, nbytes, offs):
+        ref = orclib.convert(r, want_f64=False, dither_seed=5, **kw)
+        assert np.array_equal(o.cpu().numpy()[b:b + n], ref.pcm)
+    batch.close()
