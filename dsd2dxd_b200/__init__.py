@@ -12,7 +12,7 @@ from . import _capi
 from ._capi import Config, D2PError, Job, PlanInfo  # noqa: F401
 
 __all__ = ["make_config", "plan", "frames_for_bytes", "tap_table", "tap_table_names", "device_count",
-           "Converter", "convert_host", "Batch", "D2PError", "HostBuffer", "total_frames", "block_range"]
+           "Converter", "convert_host", "Batch", "run_noalloc", "D2PError", "HostBuffer", "total_frames", "block_range"]
 
 
 def make_config(dsd_rate=1, out_rate=352800, filt="E", bits=24, dither="X", level_db=0.0, channels=2,
@@ -253,6 +253,25 @@ class Batch:
         clipped, peak = C.c_int64(), C.c_double()
         _capi.check(_capi.lib().d2p_batch_stats(self._h, C.c_void_p(stream), C.byref(clipped), C.byref(peak)))
         return {"clipped_samples": clipped.value, "peak_abs": peak.value}
+
+
+def run_noalloc(cfg, items, stream=0, want_stats=True):
+    """d2p_run_noalloc: Batch.run without a Batch, for hosts where the library must not allocate device memory (its job
+    table, LUT and statistics sit in a 256 KiB array inside the library).  items as for Batch.make_jobs; at most
+    _capi.NOALLOC_MAX_JOBS of them; no dither F.  Returns (frames per job, stats dict of this call or None).
+    Asking for the stats waits for the stream."""
+    items = list(items)
+    arr = (Job * max(len(items), 1))()
+    for j, it in zip(arr, items):
+        j.d_in, j.in_bytes = it["d_in"], it["in_bytes"]
+        j.d_out, j.out_cap_bytes = it["d_out"], it["out_cap_bytes"]
+        j.d_f64, j.f64_stride = it.get("d_f64", None), it.get("f64_stride", 0)
+        j.dither_seed = it.get("dither_seed", 0)
+    clipped, peak = C.c_int64(), C.c_double()
+    _capi.check(_capi.lib().d2p_run_noalloc(C.byref(cfg), arr, len(items), C.c_void_p(stream),
+                                            C.byref(clipped) if want_stats else None, C.byref(peak) if want_stats else None))
+    stats = {"clipped_samples": clipped.value, "peak_abs": peak.value} if want_stats else None
+    return [int(j.frames) for j in arr[:len(items)]], stats
 
 
 # ---- container front / back end (include/dsd2pcm_b200_files.h) ------------------------------------------

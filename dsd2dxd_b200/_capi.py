@@ -16,6 +16,7 @@ ERR_INVALID_ARG, ERR_TAPS_NOT_FOUND, ERR_UNSUPPORTED_LM, ERR_BIT_DEPTH = 1, 2, 3
 ERR_NO_DEVICE, ERR_CUDA, ERR_NOMEM, ERR_STATE, ERR_CAPACITY, ERR_CANCELLED = 5, 6, 7, 8, 9, 10
 PROGRESS_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_uint64, C.c_uint64)
 OUT_INTERLEAVED_LE, OUT_INTERLEAVED_BE, OUT_PLANAR_32, OUT_NONE = 0, 1, 2, 3
+NOALLOC_SCRATCH_BYTES, NOALLOC_MAX_JOBS = 256 * 1024, 64
 
 
 class Config(C.Structure):
@@ -90,7 +91,7 @@ EXPORTS = [
     "d2p_create", "d2p_destroy", "d2p_push", "d2p_flush", "d2p_set_push_threshold", "d2p_finish", "d2p_frames_ready", "d2p_pull", "d2p_pull_f64", "d2p_stats",
     "d2p_convert_host", "d2p_check_level", "d2p_host_alloc", "d2p_host_free",
     "d2p_batch_create", "d2p_batch_destroy", "d2p_batch_run", "d2p_batch_convert_host", "d2p_batch_launches",
-    "d2p_batch_stats", "d2p_batch_stats_reset", "d2p_batch_job_stats", "d2p_batch_set_control", "d2p_total_frames", "d2p_block_range", "d2p_batch_run_blocks", "d2p_debug_fpd_exponent",
+    "d2p_batch_stats", "d2p_batch_stats_reset", "d2p_batch_job_stats", "d2p_batch_set_control", "d2p_total_frames", "d2p_block_range", "d2p_batch_run_blocks", "d2p_run_noalloc", "d2p_debug_fpd_exponent",
     "d2p_container_parse", "d2p_container_open", "d2p_pcm_header", "d2p_write_pcm_file", "d2p_write_flac_file", "d2p_write_flac_file_ex", "d2p_id3_to_vorbis", "d2p_convert_file", "d2p_convert_file_ex",
 ]
 
@@ -152,6 +153,7 @@ def lib():
     L.d2p_total_frames.argtypes = [cfgp, C.c_uint64]
     L.d2p_block_range.argtypes = [cfgp, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.d2p_batch_run_blocks.argtypes = [vp, C.POINTER(BlockJob), C.c_int, vp]
+    L.d2p_run_noalloc.argtypes = [cfgp, C.POINTER(Job), C.c_int, vp, C.POINTER(C.c_int64), C.POINTER(C.c_double)]
     cip = C.POINTER(ContainerInfo)
     L.d2p_container_parse.argtypes = [vp, C.c_size_t, C.c_uint64, cip]
     L.d2p_container_open.argtypes = [C.c_char_p, cip]

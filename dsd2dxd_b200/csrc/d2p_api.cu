@@ -132,7 +132,9 @@ static LmGeom lm_geometry(const Plan& p, const LmLut& ll, int TF, int NB) {
     return g;
 }
 
-static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
+// host_lut: when given, the LUT (in its shared-memory layout) is handed back in host memory instead of being placed in
+// a device allocation of its own, and kp.lut stays null for the caller to fill (d2p_run_noalloc).
+static int build_device_plan(const d2p_config& cfg, DevicePlan** out, std::vector<double>* host_lut = nullptr) {
     std::string msg;
     std::unique_ptr<DevicePlan> dp(new DevicePlan());
     int st = make_plan(cfg, &dp->plan, &msg);
@@ -247,10 +249,13 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
                     for (int gq = 0; gq < p.gmax; ++gq)
                         sk[(size_t)b * ll.slots + (size_t)ll.Gp * (u + ll.A * cy) + gq] = lut[((size_t)ph * p.gmax + gq) * 256 + b];
                 }
-        CK(cudaMalloc(&dp->d_lut, sk.size() * sizeof(double)));
-        CK(cudaMemcpy(dp->d_lut, sk.data(), sk.size() * sizeof(double), cudaMemcpyHostToDevice));
+        if (!host_lut) {
+            CK(cudaMalloc(&dp->d_lut, sk.size() * sizeof(double)));
+            CK(cudaMemcpy(dp->d_lut, sk.data(), sk.size() * sizeof(double), cudaMemcpyHostToDevice));
+        }
         k.lut = dp->d_lut;
         k.lut_doubles = (int)sk.size();
+        if (host_lut) host_lut->swap(sk);
     } else {
         // integer path: pick the replication (skew depth K) and the tile size together.  More replicas mean
         // fewer idle skew steps per frame (nt / (nt + K - 1)) but a larger LUT; one persistent CTA per SM.
@@ -296,10 +301,13 @@ static int build_device_plan(const d2p_config& cfg, DevicePlan** out) {
             for (int r = 0; r < L.R; ++r)
                 for (int i = 0; i < p.nt; ++i)
                     sk[(size_t)b * L.slots + L.st[r] + i] = lut[(size_t)i * 256 + b];
-        CK(cudaMalloc(&dp->d_lut, sk.size() * sizeof(double)));
-        CK(cudaMemcpy(dp->d_lut, sk.data(), sk.size() * sizeof(double), cudaMemcpyHostToDevice));
+        if (!host_lut) {
+            CK(cudaMalloc(&dp->d_lut, sk.size() * sizeof(double)));
+            CK(cudaMemcpy(dp->d_lut, sk.data(), sk.size() * sizeof(double), cudaMemcpyHostToDevice));
+        }
         k.lut = dp->d_lut;
         k.lut_doubles = (int)sk.size();
+        if (host_lut) host_lut->swap(sk);
     }
     if (!dp->lm) {
         // |y| <= sum |H| for a +-1 input, so |y*scale| + dither + rounding stays far inside i32 for every sane level
@@ -1316,6 +1324,106 @@ int d2p_batch_run_blocks(d2p_batch* b, const d2p_block_job* jobs, int njobs, voi
 }
 
 uint64_t d2p_batch_launches(const d2p_batch* b) { return b ? b->launcher.launches : 0; }
+
+// ---- conversion without any allocation ------------------------------------------------------------------
+// d2p_batch_run for callers that may not allocate device memory (see the header for who they are).  What the batch
+// object would have cudaMalloc'ed -- statistics record, job table, LUT -- lives in the scratch array built into the
+// module (d2p_kernels.cu); this function only writes it, on the caller's stream, in front of the launch.  Nothing in
+// here, nor in what it calls, allocates or frees device or pinned memory; host-side work uses the ordinary heap.
+int d2p_run_noalloc(const d2p_config* cfg, d2p_job* jobs, int njobs, void* cuda_stream,
+                    int64_t* clipped_samples, double* peak_abs) {
+    if (!cfg || (!jobs && njobs) || njobs < 0) return set_err(D2P_ERR_INVALID_ARG, "null argument");
+    if (njobs > kNoallocMaxJobs) {
+        char buf[160];
+        std::snprintf(buf, sizeof buf, "d2p_run_noalloc: %d jobs in one call, the built-in job table holds %d (D2P_NOALLOC_MAX_JOBS)",
+                      njobs, kNoallocMaxJobs);
+        return set_err(D2P_ERR_CAPACITY, buf);
+    }
+    if (cfg->dither == D2P_DITHER_FPD)
+        return set_err(D2P_ERR_INVALID_ARG, "d2p_run_noalloc: dither F keeps 4 bytes of generator state per output sample and a "
+                                            "4 MiB jump table on the device; the built-in scratch has no room for them");
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    std::vector<double> lut;
+    DevicePlan* raw_dp = nullptr;
+    int st = build_device_plan(*cfg, &raw_dp, &lut);             // sets the device; places nothing on it
+    if (st != D2P_OK) return st;
+    std::unique_ptr<DevicePlan> dp(raw_dp);
+    const Plan& p = dp->plan;
+    const d2p_config& c = p.cfg;
+    const size_t lut_bytes = lut.size() * sizeof(double);
+    if (lut_bytes > kNoallocScratchBytes - kNoallocLutOffset) {
+        char buf[160];
+        std::snprintf(buf, sizeof buf, "d2p_run_noalloc: filter LUT of %zu bytes exceeds the %zu bytes of built-in scratch",
+                      lut_bytes, kNoallocScratchBytes - kNoallocLutOffset);
+        return set_err(D2P_ERR_CAPACITY, buf);
+    }
+
+    // the same job description as d2p_batch_run: one whole payload per job
+    const bool planar = c.in_layout == D2P_LAYOUT_PLANAR;
+    const size_t G = group_bytes(c);
+    const long long unit = planar ? (long long)c.block_size : 1;
+    const size_t fb = c.out_format == D2P_OUT_NONE ? 0 : (size_t)c.channels * (c.out_format == D2P_OUT_PLANAR_32 ? 4 : p.bps);
+    DevJob live[kNoallocMaxJobs];
+    int nlive = 0;
+    unsigned long long tiles = 0;
+    bool fast = dp->fast_writer;
+    for (int i = 0; i < njobs; ++i) {
+        d2p_job& u = jobs[i];
+        const long long groups = (long long)(u.in_bytes / G);
+        const long long tail_per = (long long)((u.in_bytes - (size_t)groups * G) / c.channels);
+        const long long total_q = groups * unit + tail_per;
+        const long long nf = p.frames_for_bytes(total_q);
+        if ((size_t)nf * fb > u.out_cap_bytes) return set_err(D2P_ERR_CAPACITY, "job output buffer too small");
+        if (u.d_f64 && (long long)u.f64_stride < nf) return set_err(D2P_ERR_CAPACITY, "job f64 stride too small");
+        u.frames = (uint64_t)nf;
+        if (nf <= 0) continue;
+        DevJob& j = live[nlive++];
+        std::memset(&j, 0, sizeof j);
+        j.in = (const uint8_t*)u.d_in; j.base_q = 0; j.end_q = total_q;
+        j.tail_q = (planar && tail_per > 0) ? groups * unit : LLONG_MAX; j.tail_len = tail_per;
+        j.f_begin = 0; j.f_count = nf;
+        j.out = (uint8_t*)u.d_out; j.out_stride = nf;
+        j.f64 = u.d_f64; j.f64_stride = (long long)u.f64_stride;
+        j.seed = u.dither_seed; j.total_q = total_q;
+        j.job_id = i;
+        j.tile_begin = (unsigned int)tiles;
+        tiles += (unsigned long long)((nf + dp->kp.TF - 1) / dp->kp.TF);
+        if (u.d_f64) fast = false;
+    }
+    if (tiles > 0xFFFFFFF0ull) return set_err(D2P_ERR_INVALID_ARG, "too many tiles in one launch");
+
+    void* base = nullptr;
+    CK(noalloc_scratch_address(&base));                          // first call on a device: looks the array up
+    unsigned char* scratch = (unsigned char*)base;
+    DevStats* d_stats = (DevStats*)scratch;
+    // the array still holds whatever the previous call left: the statistics must start from zero, job table and LUT
+    // are overwritten in full for the part this launch reads
+    CK(cudaMemsetAsync(d_stats, 0, sizeof(DevStats), stream));
+    if (tiles) {
+        // pageable sources: the runtime has taken its copy of `live` and `lut` when these calls return
+        CK(cudaMemcpyAsync(scratch + kNoallocJobsOffset, live, sizeof(DevJob) * nlive, cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(scratch + kNoallocLutOffset, lut.data(), lut_bytes, cudaMemcpyHostToDevice, stream));
+        KParams k = dp->kp;
+        k.lut = (const double*)(scratch + kNoallocLutOffset);
+        k.jobs = (const DevJob*)(scratch + kNoallocJobsOffset);
+        k.njobs = nlive;
+        k.total_tiles = (unsigned int)tiles;
+        k.stats = d_stats;
+        k.job_stats = nullptr; k.events = nullptr; k.ev_cap = 0;
+        k.fpd_jump = nullptr; k.fpd_items = 0;
+        const unsigned long long want = (unsigned long long)dp->num_sms * dp->ctas_per_sm;
+        const int grid = (int)std::min<unsigned long long>(tiles, want);
+        CK(launch_kernels(k, kernel_variant(k, dp->lm, fast), grid, dp->threads, dp->smem, stream));
+    }
+    if (clipped_samples || peak_abs) {
+        DevStats hs;
+        CK(cudaMemcpyAsync(&hs, d_stats, sizeof hs, cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        if (clipped_samples) *clipped_samples = (int64_t)(hs.clip_lo + hs.clip_hi);
+        if (peak_abs) std::memcpy(peak_abs, &hs.peak_bits, 8);
+    }
+    return D2P_OK;
+}
 
 int d2p_debug_fpd_exponent(const double* samples, int n, int32_t* exponents, int device) {
     if ((!samples || !exponents) && n > 0) return set_err(D2P_ERR_INVALID_ARG, "null argument");

@@ -18,6 +18,8 @@
 #include <limits.h>
 #include <stdint.h>
 
+#include <mutex>
+
 #include "d2p_device.h"
 #include "d2p_launch.h"
 
@@ -1242,6 +1244,38 @@ cudaError_t launch_fpd(const KParams& P, cudaStream_t stream) {
     if (!P.fpd_items) return cudaSuccess;
     fpd_kernel<<<(P.fpd_items + 255) / 256, 256, 0, stream>>>(P);
     return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// built-in scratch of d2p_run_noalloc (include/dsd2pcm_b200.h)
+// ------------------------------------------------------------------------------------------------
+// The kernels read three things from global memory that are neither the caller's input nor its output: the job table,
+// the filter LUT (copied into shared memory by every CTA) and the statistics record.  Everywhere else the host side
+// cudaMallocs them.  This array is the same storage reserved inside the module image instead, for callers that must
+// not allocate: it exists on every device that loads this library, from module load until the process ends, and all
+// calls of d2p_run_noalloc on a device share it.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoallocScratchBytes];
+
+// Device address of g_noalloc_scratch on the CURRENT device.  In host code the name g_noalloc_scratch is only a handle
+// for the runtime's symbol table -- a kernel handed `g_noalloc_scratch` itself would not be looking at this array -- so
+// the address is asked for once per device (cudaGetSymbolAddress also makes sure the module is loaded there) and kept.
+cudaError_t noalloc_scratch_address(void** ptr) {
+    static std::mutex mu;
+    static void* per_device[64] = {};
+    *ptr = nullptr;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(mu);
+    if (!per_device[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        per_device[dev] = p;
+    }
+    *ptr = per_device[dev];
+    return cudaSuccess;
 }
 
 cudaError_t launch_kernels(const KParams& P, int variant, int grid, int threads, size_t smem, cudaStream_t stream) {

@@ -25,6 +25,17 @@ static const int kLmConsumers = 896;
 static const int kLmThreads = kLmConsumers + kLmProducers;
 static const int kMaxSmem = 227 * 1024;      // opt-in dynamic shared memory per CTA on sm_100a
 
+// Scratch built into the module for d2p_run_noalloc (d2p_kernels.cu: g_noalloc_scratch), cut up as
+//   [0, 256)                      DevStats
+//   [256, kNoallocLutOffset)      job table: kNoallocMaxJobs DevJob records
+//   [kNoallocLutOffset, end)      stage-1 LUT in its shared-memory layout (never more than kMaxSmem)
+static const size_t kNoallocScratchBytes = 256 * 1024;
+static const int    kNoallocMaxJobs = 64;
+static const size_t kNoallocJobsOffset = 256;
+static const size_t kNoallocLutOffset = (kNoallocJobsOffset + kNoallocMaxJobs * sizeof(DevJob) + 255) / 256 * 256;
+static_assert(kNoallocLutOffset + kMaxSmem <= kNoallocScratchBytes, "every LUT that fits shared memory fits the scratch");
+cudaError_t noalloc_scratch_address(void** ptr);         // device address of the scratch on the current device
+
 const char* kernel_name(bool lm);
 void lutfir_set_shape(int bpo, int* F, int* DW);          // frames per lane set / word distance the kernels are built for
 int max_ctas_per_sm(bool lm, int threads, size_t smem);   // occupancy of the kernel at this geometry (0 on error)

@@ -220,6 +220,44 @@ typedef struct d2p_block_job {
 } d2p_block_job;
 int  d2p_batch_run_blocks(d2p_batch* b, const d2p_block_job* jobs, int njobs, void* cuda_stream);
 
+/* ---- device-resident conversion that allocates nothing ------------------------------------------- */
+/* No counterpart in the reference (a CPU program has no device allocator to stay away from); it is d2p_batch_run for
+ * hosts in which this library is not allowed to obtain memory from the CUDA allocator:
+ *   - an application that gave the whole of HBM to an arena of its own, or runs under a fixed device-memory budget it
+ *     accounts for itself (a mastering or transcoding service sharing the GPU with other work): a cudaMalloc made
+ *     behind its back either fails or breaks that accounting, and d2p_batch_create makes several;
+ *   - a caller that keeps other streams busy on the same GPU (playback, metering) and cannot afford the device-wide
+ *     stall cudaMalloc / cudaFree may cause, nor their unbounded latency;
+ *   - a worker that has to finish its files after the device has run out of memory.
+ * The caller passes device pointers for input and output exactly as for d2p_batch_run.  What a d2p_batch would have
+ * allocated besides -- job table, filter look-up table, statistics record -- lives in an array of
+ * D2P_NOALLOC_SCRATCH_BYTES (256 KiB) compiled into the library; every GPU that loads the library carries that array
+ * until the process exits, whether this entry point is used or not.  The call makes no cudaMalloc, cudaFree,
+ * cudaMallocHost or any other allocating CUDA call (ordinary host heap use, such as building the filter table,
+ * remains).
+ *
+ * Limits, each refused with a message in d2p_last_error(): at most D2P_NOALLOC_MAX_JOBS jobs per call
+ * (D2P_ERR_CAPACITY); a filter table larger than the scratch (D2P_ERR_CAPACITY; none of the reference's filters is);
+ * dither F (D2P_ERR_INVALID_ARG: it needs per-sample generator state on the device).  Payload sizes are not limited.
+ *
+ * jobs[i].frames is filled as by d2p_batch_run and the launch is asynchronous on `cuda_stream`.  clipped_samples /
+ * peak_abs (either may be NULL) receive what d2p_batch_stats would report for THIS call alone; asking for either makes
+ * the call wait for the stream.
+ *
+ * First call on a device: the library looks up the device address of its array there (cudaGetSymbolAddress, which
+ * also loads the module on that device).  Make that first call -- any small conversion will do -- before beginning a
+ * stream capture on that device; later calls only enqueue work on the stream.
+ *
+ * Sharing: all calls on one device use the same array, and it keeps what the last call wrote.  The entry point
+ * re-zeroes the statistics and rewrites job table and filter table on the caller's stream every time, so back-to-back
+ * calls on ONE stream are ordered and safe, with the same or with different configurations.  Two calls whose GPU work
+ * can overlap -- different streams without an event between them, or different host threads -- overwrite each
+ * other's tables while kernels read them: that is a data race, and the PCM of both is undefined.  Serialise them. */
+#define D2P_NOALLOC_SCRATCH_BYTES (256 * 1024)
+#define D2P_NOALLOC_MAX_JOBS 64
+int  d2p_run_noalloc(const d2p_config* cfg, d2p_job* jobs, int njobs, void* cuda_stream,
+                     int64_t* clipped_samples, double* peak_abs);
+
 /* ---- diagnostics --------------------------------------------------------------------------------- */
 /* The octave step of the float dither, `s.abs().log2().floor() as i32` (Dither::fpdither, rd/dither.rs:102-104), as
  * the kernels evaluate it, on n host samples: exponents[i] receives the value for samples[i].  Exists so that the one

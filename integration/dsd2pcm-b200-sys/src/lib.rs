@@ -226,6 +226,10 @@ extern "C" {
     pub fn d2p_batch_create(cfg: *const d2p_config, out: *mut *mut d2p_batch) -> c_int;
     pub fn d2p_batch_destroy(b: *mut d2p_batch);
     pub fn d2p_batch_run(b: *mut d2p_batch, jobs: *mut d2p_job, njobs: c_int, cuda_stream: *mut c_void) -> c_int;
+    // no counterpart in the reference: d2p_batch_run for hosts where this library may not allocate device memory
+    // (scratch is a 256 KiB array inside the library; at most 64 jobs per call; calls that overlap on the GPU race)
+    pub fn d2p_run_noalloc(cfg: *const d2p_config, jobs: *mut d2p_job, njobs: c_int, cuda_stream: *mut c_void,
+                           clipped_samples: *mut i64, peak_abs: *mut f64) -> c_int;
     pub fn d2p_batch_convert_host(b: *mut d2p_batch, raw: *const u8, nbytes: usize, pcm: *mut c_void, out_cap_bytes: usize,
                                   frames: *mut u64) -> c_int;
     pub fn d2p_batch_launches(b: *const d2p_batch) -> u64;
