@@ -295,21 +295,27 @@ int d2p_write_pcm_file(const char* path, int container, int bits, int channels, 
 
 // The tag as an "ID3 " chunk behind the sample data of a RIFF / FORM file (what Tag::write_to_path does for WAV and
 // AIFF files): chunk id, size (little-endian in RIFF, big-endian in FORM), blob, pad byte to an even length; the
-// container's own size field grows by the same amount.
-static int append_id3_chunk(const char* path, bool riff, const std::vector<uint8_t>& tag) {
+// container's own size field grows by the same amount.  The PCM writers leave out the pad byte behind an odd-sized
+// data / SSND chunk (the reference's quirk, see the file header) -- harmless while that chunk is the last one, but a
+// chunk that follows must start on an even offset or RIFF / IFF readers, which skip the pad, land one byte into it:
+// an odd-length file gets the missing pad first (mono or 3- / 5-channel 24-bit output with an odd frame count).
+static int append_id3_chunk(const char* path, bool riff, const std::vector<uint8_t>& tag, uint64_t* added) {
     FileCloser f{std::fopen(path, "rb+")};
     if (!f.f) return api_set_error(D2P_ERR_INVALID_ARG, "cannot reopen the output file for the tag chunk");
     uint8_t head[8];
     if (std::fread(head, 1, 8, f.f) != 8) return api_set_error(D2P_ERR_INVALID_ARG, "short output file");
+    if (std::fseek(f.f, 0, SEEK_END) != 0) return api_set_error(D2P_ERR_INVALID_ARG, "write failed");
+    const uint32_t pre = (uint32_t)(std::ftell(f.f) & 1);
     const uint32_t n = (uint32_t)tag.size(), padded = (n + 1) & ~1u;
     uint32_t total = riff ? le32(head + 4) : be32(head + 4);
-    total += 8 + padded;
+    total += pre + 8 + padded;
     uint8_t ch[8] = {'I', 'D', '3', ' ', 0, 0, 0, 0}, sz[4];
     for (int i = 0; i < 4; ++i) { ch[4 + i] = (uint8_t)(riff ? n >> (8 * i) : n >> (8 * (3 - i))); sz[i] = (uint8_t)(riff ? total >> (8 * i) : total >> (8 * (3 - i))); }
     const uint8_t zero = 0;
-    if (std::fseek(f.f, 0, SEEK_END) != 0 || std::fwrite(ch, 1, 8, f.f) != 8 || std::fwrite(tag.data(), 1, n, f.f) != n ||
+    if ((pre && std::fwrite(&zero, 1, 1, f.f) != 1) || std::fwrite(ch, 1, 8, f.f) != 8 || std::fwrite(tag.data(), 1, n, f.f) != n ||
         (padded != n && std::fwrite(&zero, 1, 1, f.f) != 1) || std::fseek(f.f, 4, SEEK_SET) != 0 || std::fwrite(sz, 1, 4, f.f) != 4)
         return api_set_error(D2P_ERR_INVALID_ARG, "write failed");
+    if (added) *added = (uint64_t)pre + 8 + padded;
     return D2P_OK;
 }
 
@@ -418,6 +424,7 @@ int d2p_convert_file_ex(const d2p_file_options* opt, const char* in_path, const 
     };
 
     uint64_t frames = 0;
+    uint64_t tag_chunk_bytes = 0;                                  // "ID3 " chunk behind the samples, pads included
     if (opt->out_container == D2P_FILE_FLAC) {
         // The FLAC encoder wants the whole stream (STREAMINFO totals, MD5): payload and PCM are held in pinned memory and
         // go through the pipelined whole-payload conversion.
@@ -497,7 +504,7 @@ int d2p_convert_file_ex(const d2p_file_options* opt, const char* in_path, const 
         if ((st = d2p_stats(ctx, &clips, &R.peak_abs, &R.clipped_samples)) != D2P_OK) return fail(st);
         if (std::fflush(of.f) != 0) return fail(api_set_error(D2P_ERR_INVALID_ARG, "write failed"));
         of.close();
-        if (!id3.empty() && opt->out_container != D2P_FILE_RAW && (st = append_id3_chunk(out_path, opt->out_container == D2P_FILE_WAV, id3)) != D2P_OK)
+        if (!id3.empty() && opt->out_container != D2P_FILE_RAW && (st = append_id3_chunk(out_path, opt->out_container == D2P_FILE_WAV, id3, &tag_chunk_bytes)) != D2P_OK)
             return fail(st);
     }
     R.frames = frames;
@@ -510,7 +517,7 @@ int d2p_convert_file_ex(const d2p_file_options* opt, const char* in_path, const 
     Bytes h;
     build_header(opt->out_container, opt->bits, ci.channels, opt->out_rate, frames, &h);
     R.out_bytes = h.v.size() + frames * (uint64_t)ci.channels * (uint64_t)pi.bytes_per_sample;
-    if (!id3.empty() && opt->out_container != D2P_FILE_RAW) R.out_bytes += 8 + ((id3.size() + 1) & ~(size_t)1);
+    R.out_bytes += tag_chunk_bytes;
     return D2P_OK;
 }
 

@@ -89,11 +89,38 @@ void put_utf8(std::string& o, uint32_t c) {
     else { o.push_back((char)(0xF0 | (c >> 18))); o.push_back((char)(0x80 | ((c >> 12) & 0x3F))); o.push_back((char)(0x80 | ((c >> 6) & 0x3F))); o.push_back((char)(0x80 | (c & 0x3F))); }
 }
 
+// Bytes that claim to be UTF-8 -> valid UTF-8: every maximal ill-formed subsequence becomes one U+FFFD (what
+// String::from_utf8_lossy and Python's errors="replace" do).  FLAC requires Vorbis comments to be UTF-8.
+std::string utf8_lossy(const uint8_t* p, size_t n) {
+    std::string o;
+    size_t i = 0;
+    while (i < n) {
+        const uint8_t b = p[i];
+        if (b < 0x80) { o.push_back((char)b); ++i; continue; }
+        int need = 0; uint8_t lo = 0x80, hi = 0xBF;                // bounds of the second byte (Unicode table 3-7)
+        if (b >= 0xC2 && b <= 0xDF) need = 1;
+        else if (b == 0xE0) { need = 2; lo = 0xA0; }
+        else if (b == 0xED) { need = 2; hi = 0x9F; }               // no surrogates
+        else if (b >= 0xE1 && b <= 0xEF) need = 2;
+        else if (b == 0xF0) { need = 3; lo = 0x90; }
+        else if (b >= 0xF1 && b <= 0xF3) need = 3;
+        else if (b == 0xF4) { need = 3; hi = 0x8F; }
+        size_t j = i + 1;
+        int k = 0;
+        for (; k < need && j < n; ++k, ++j)
+            if (p[j] < (k == 0 ? lo : 0x80) || p[j] > (k == 0 ? hi : 0xBF)) break;
+        if (need && k == need) o.append((const char*)p + i, j - i);
+        else put_utf8(o, 0xFFFD);
+        i = j;
+    }
+    return o;
+}
+
 // one encoded string [p, p+n) -> UTF-8 (embedded NULs kept: multi-value frames are split by the caller)
 std::string decode(int enc, const uint8_t* p, size_t n) {
     std::string o;
     if (enc == 0) { for (size_t i = 0; i < n; ++i) put_utf8(o, p[i]); return o; }
-    if (enc == 3) return std::string((const char*)p, n);
+    if (enc == 3) return utf8_lossy(p, n);
     bool be = enc == 2;
     size_t i = 0;
     if (enc == 1 && n >= 2) {
@@ -106,6 +133,7 @@ std::string decode(int enc, const uint8_t* p, size_t n) {
             const uint32_t d = be ? ((uint32_t)p[i + 2] << 8) | p[i + 3] : ((uint32_t)p[i + 3] << 8) | p[i + 2];
             if (d >= 0xDC00 && d < 0xE000) { c = 0x10000 + ((c - 0xD800) << 10) + (d - 0xDC00); i += 2; }
         }
+        if (c >= 0xD800 && c < 0xE000) c = 0xFFFD;                 // a surrogate without its partner
         put_utf8(o, c);
     }
     return o;
@@ -241,7 +269,7 @@ void to_vorbis(const Tag& t, std::vector<std::string>* out) {
         if (f.id == "UFID") {
             const size_t z = std::find(f.body.begin(), f.body.end(), (uint8_t)0) - f.body.begin();
             if (z < f.body.size() && std::string((const char*)f.body.data(), z) == "http://musicbrainz.org")
-                ins("MUSICBRAINZ_TRACKID", std::string((const char*)f.body.data() + z + 1, f.body.size() - z - 1));
+                ins("MUSICBRAINZ_TRACKID", utf8_lossy(f.body.data() + z + 1, f.body.size() - z - 1));
         }
     for (const auto& w : {std::make_pair("WCOP", "LICENSE"), std::make_pair("WOAR", "WEBSITE")}) {   // :552-560
         const Frame* f = find(t, w.first);
@@ -319,7 +347,9 @@ bool append_album(std::vector<uint8_t>* blob, const char* suffix) {
     size_t q = 10;
     while (q + 10 <= 10 + size && b[q] != 0) {
         const size_t fs = t.major == 4 ? syncsafe(b + q + 4) : be32(b + q + 4);
-        if (std::memcmp(b + q, "TALB", 4) == 0 && fs >= 1 && !(b[q + 9] & 0x0F)) {
+        // format flags that change the frame body (compression, encryption, grouping byte, unsynchronisation, data
+        // length indicator) sit in different bits in v2.3 and v2.4: such a frame is left as it is
+        if (std::memcmp(b + q, "TALB", 4) == 0 && fs >= 1 && !(b[q + 9] & (t.major == 4 ? 0x4F : 0xE0))) {
             const int enc = b[q + 10];
             std::vector<uint8_t> body(b + q + 10, b + q + 10 + fs);
             while (body.size() > 1 && body.back() == 0 && (enc == 0 || enc == 3)) body.pop_back();

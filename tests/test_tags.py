@@ -46,6 +46,26 @@ def rich_tag(major, enc):
     return T.make_tag(frames, major=major, padding=64)
 
 
+def test_malformed_text_still_gives_utf8_comments():
+    """FLAC wants UTF-8 Vorbis comments: ill-formed UTF-8 and surrogates without a partner become U+FFFD (one per maximal
+    ill-formed run, as String::from_utf8_lossy and Python's errors="replace" put them)."""
+    u16 = lambda units, big: b"".join(struct.pack(">H" if big else "<H", u) for u in units)
+    frames = [
+        ("TIT2", b"\x03" + b"ok \xff\xfe stray, \xe2\x82 cut short, \xed\xa0\x80 surrogate, \xc0\xaf overlong, \xf4\x90\x80\x80 too big, fine: \xe6\xa8\x99"),
+        ("TALB", b"\x01\xff\xfe" + u16([0x41, 0xD800, 0x42, 0xDC00, 0x43, 0xD83D, 0xDE00, 0xD800], False)),
+        ("TPE1", b"\x02" + u16([0xDC00, 0x61, 0xD800, 0xD800, 0xDC00], True)),
+        ("TCON", b"\x03tail \xe6\xa8"),
+        ("UFID", b"http://musicbrainz.org\0" + b"id-\xff-\xe2\x82"),
+    ]
+    blob = T.make_tag(frames, major=4, padding=16)
+    want = T.id3_to_vorbis(blob)
+    got = d2p.id3_to_vorbis(blob)                               # the wrapper decodes strictly: invalid bytes would raise
+    assert got == want
+    assert "ALBUM=A\ufffdB\ufffdC\U0001F600\ufffd" in got and "ARTIST=\ufffda\ufffd\U00010000" in got
+    assert any(c.startswith("TITLE=ok \ufffd\ufffd stray, \ufffd cut short, \ufffd\ufffd\ufffd surrogate") for c in got)
+    assert "GENRE=tail \ufffd" in got and "MUSICBRAINZ_TRACKID=id-\ufffd-\ufffd" in got
+
+
 @pytest.mark.parametrize("major", [3, 4])
 @pytest.mark.parametrize("enc", [0, 1, 3] + [2])
 def test_id3_to_vorbis_mapping_matches_the_reference_table(major, enc):
@@ -130,6 +150,65 @@ def test_pcm_files_carry_the_tag_as_an_id3_chunk(tmp_path, fixtures, container):
     n = int.from_bytes(chunk[4:8], "little" if container == "W" else "big")
     got = T.id3_to_vorbis(chunk[8: 8 + n])
     assert got == [c + " [176.4K]" if c.startswith("ALBUM=") else c for c in T.id3_to_vorbis(blob)]
+
+
+def _walk_chunks(data, little, ssnd_short=False):
+    """Chunks of a RIFF / FORM file the way a conformant reader finds them: every chunk starts on an even offset.
+    ssnd_short: the reference's AIFF writer leaves the 8 offset / blockSize bytes out of SSND's size field."""
+    assert int.from_bytes(data[4:8], "little" if little else "big") == len(data) - 8
+    at, out = 12, {}
+    while at + 8 <= len(data):
+        n = int.from_bytes(data[at + 4: at + 8], "little" if little else "big")
+        out[bytes(data[at: at + 4])] = (at + 8, n)
+        if ssnd_short and data[at: at + 4] == b"SSND":
+            n += 8
+        at += 8 + n + (n & 1)
+    assert at in (len(data), len(data) + 1)      # the reference leaves out the pad behind a LAST odd chunk (bare files)
+    return out
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("container", ["W", "A", "C"])
+def test_tag_chunk_behind_an_odd_sized_payload_starts_on_an_even_offset(tmp_path, fixtures, container):
+    """Mono 24-bit with an odd frame count: the sample chunk has an odd size and no pad of its own."""
+    blob = rich_tag(3, 1)
+    pay = fixtures["1kHz_mono_p"][0].tobytes()
+    src = tmp_path / "mono.dsf"
+    src.write_bytes(orc.make_dsf(pay, 1, 1, id3=blob))
+    dst = tmp_path / "o.bin"
+    res = d2p.convert_file(src, dst, out_rate=352800, bits=24, container=container, copy_tags=True)
+    assert res["frames"] % 2 == 1
+    ref = orclib.convert(np.frombuffer(pay, dtype=np.uint8), dsd_rate=1, out_rate=352800, bits=24, channels=1, stdout_mode=False, want_f64=False)
+    bare = orc.WRITERS[container](ref.planar, 24, 352800)
+    data = dst.read_bytes()
+    assert len(bare) % 2 == 1 and data[8: len(bare)] == bare[8:]
+    assert res["out_bytes"] == len(data) == len(bare) + 1 + 8 + len(blob) + len(blob) % 2
+    chunks = _walk_chunks(data, container == "W", container == "A")
+    at, n = chunks[b"ID3 "]
+    assert at % 2 == 0 and data[at: at + n] == blob
+    sample_chunk = b"data" if container == "W" else b"SSND"
+    assert sample_chunk in chunks and _walk_chunks(bare, container == "W", container == "A").keys() == chunks.keys() - {b"ID3 "}
+
+
+@pytest.mark.gpu
+def test_album_suffix_leaves_frames_with_body_changing_flags_alone(tmp_path, fixtures):
+    """-a rewrites TALB in place; a compressed / encrypted / grouped frame (bits 0x80 / 0x40 / 0x20 of the second flag
+    byte in v2.3; 0x08 / 0x04 / 0x40, and 0x02 / 0x01, in v2.4) does not hold plain text: the tag is copied unchanged."""
+    def chunk_of(blob, name):
+        src, _ = _dsf_with_tag(tmp_path, fixtures, blob, name)
+        dst = tmp_path / "o.wav"
+        d2p.convert_file(src, dst, out_rate=176400, bits=16, container="W", copy_tags=True, append_rate=True)
+        data = dst.read_bytes()
+        at, n = _walk_chunks(data, True)[b"ID3 "]
+        return data[at: at + n]
+    for major, bits in ((3, (0x80, 0x40, 0x20)), (4, (0x08, 0x04, 0x40, 0x02, 0x01))):
+        blob = T.make_tag([T.text_frame("TALB", "The Album", 0), T.text_frame("TIT2", "t", 0)], major=major, padding=8)
+        assert blob[10:14] == b"TALB"
+        plain = chunk_of(blob, f"p{major}.dsf")
+        assert plain != blob and b"The Album [176.4K]" in plain
+        for bit in bits:
+            flagged = blob[:19] + bytes([bit]) + blob[20:]
+            assert chunk_of(flagged, f"f{major}_{bit}.dsf") == flagged, (major, hex(bit))
 
 
 @pytest.mark.gpu
