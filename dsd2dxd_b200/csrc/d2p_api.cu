@@ -413,6 +413,7 @@ struct Launcher {
     size_t fpd_cap[kRing] = {0, 0, 0, 0};
     uint64_t launches = 0;
     bool want_jobstats = false;                                      // batch objects: peak / clipped samples per job
+    bool use_jobstats = false;                                       // ... for the run in progress
     DevJobStats* d_jobstats = nullptr;
     int jobstats_cap = 0, jobstats_n = 0;
 
@@ -438,9 +439,14 @@ struct Launcher {
     // Dither F needs 4 bytes of xorshift state per output sample of a launch: long jobs are cut into pieces of at
     // most kFpdSamples samples, launched one group after the other on the same stream (the buffer is reused).
     static const long long kFpdSamples = 256ll << 20;
-    int run(const DevicePlan& dp, std::vector<DevJob>& jobs, cudaStream_t stream) {
+    // per_job: keep the per-job table for this run (d2p_batch_run / d2p_batch_run_blocks).  The pipelined host
+    // conversion drives one launcher on three streams and must not: a memset of the shared table on one stream would
+    // race with the kernels of the other two, and nobody reads per-job figures of pipeline chunks.
+    int run(const DevicePlan& dp, std::vector<DevJob>& jobs, cudaStream_t stream, bool per_job = true) {
         for (size_t i = 0; i < jobs.size(); ++i) jobs[i].job_id = (int)i;
-        if (want_jobstats) {                                         // table of the most recent run, indexed by job
+        use_jobstats = want_jobstats && per_job;
+        if (!use_jobstats) jobstats_n = 0;                           // a later d2p_batch_job_stats fails cleanly
+        if (use_jobstats) {                                          // table of the most recent run, indexed by job
             if (jobstats_cap < (int)jobs.size()) {
                 if (d_jobstats) cudaFree(d_jobstats);
                 jobstats_cap = (int)jobs.size() + 16;
@@ -531,7 +537,7 @@ struct Launcher {
         k.njobs = (int)live.size();
         k.total_tiles = (unsigned int)tiles;
         k.stats = d_stats;
-        k.job_stats = want_jobstats ? d_jobstats : nullptr;
+        k.job_stats = use_jobstats ? d_jobstats : nullptr;
         k.events = d_events;
         k.ev_cap = d_events ? kEventCap : 0;
         const unsigned long long want = (unsigned long long)dp.num_sms * dp.ctas_per_sm;
@@ -1118,7 +1124,7 @@ static int host_convert(const DevicePlan& dp, Launcher& launcher, HostPipe& pipe
             j.f_begin = f_done; j.f_count = f_new - f_done;
             j.out = pipe.d_out[s]; j.seed = c.dither_seed; j.total_q = total_q;
             if ((size_t)j.f_count * fb > pipe.out_cap) { rc = set_err(D2P_ERR_NOMEM, "internal: chunk output larger than staging buffer"); break; }
-            if ((rc = launcher.run(dp, jobs, pipe.streams[s])) != D2P_OK) break;
+            if ((rc = launcher.run(dp, jobs, pipe.streams[s], false)) != D2P_OK) break;
             if (!no_pcm) {
                 e = cudaMemcpyAsync((uint8_t*)pcm + (size_t)f_done * fb, pipe.d_out[s], (size_t)j.f_count * fb, cudaMemcpyDeviceToHost, pipe.streams[s]);
                 if (e != cudaSuccess) { rc = cuda_err(e, "D2H"); break; }

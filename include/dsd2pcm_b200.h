@@ -192,7 +192,8 @@ uint64_t d2p_batch_launches(const d2p_batch* b);
 int  d2p_batch_stats(d2p_batch* b, void* cuda_stream, int64_t* clipped_samples, double* peak_abs);
 int  d2p_batch_stats_reset(d2p_batch* b, void* cuda_stream);
 /* Per job of the most recent d2p_batch_run / d2p_batch_run_blocks (dsd_levels reports one peak per file,
- * src/bin/dsd_levels/main.rs:207): arrays of njobs entries, either may be NULL.  Synchronises the stream. */
+ * src/bin/dsd_levels/main.rs:207): arrays of njobs entries, either may be NULL.  Synchronises the stream.
+ * d2p_batch_convert_host keeps no per-job table: after it, njobs > 0 is refused with D2P_ERR_INVALID_ARG. */
 int  d2p_batch_job_stats(d2p_batch* b, void* cuda_stream, int njobs, int64_t* clipped_samples, double* peak_abs);
 
 /* ---- time-block split of one long payload -------------------------------------------- */

@@ -168,6 +168,12 @@ def test_per_job_peaks_for_level_batches():
     assert batch.stats(stream)["peak_abs"] == max(refs)
     batch.stats_reset(stream)
     assert batch.stats(stream)["peak_abs"] == 0.0
+    # the pipelined host conversion keeps no per-job table (its chunks are not the caller's jobs): asking says so
+    batch.convert_host(raws[0], np.zeros(0, dtype=np.uint8))
+    with pytest.raises(_capi.D2PError) as e:
+        batch.job_stats(1, stream)
+    assert e.value.status == _capi.ERR_INVALID_ARG
+    assert batch.stats(stream)["peak_abs"] == refs[0]
     batch.close()
 
 
