@@ -365,27 +365,33 @@ def main():
     th_in, th_out = torch.from_numpy(h_in.array), torch.from_numpy(h_out.array)
     cs = [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)]
 
+    e2e_files_rank = max(1, max(len(x) for x in shard.assign_files([1] * args.e2e_total_files, world)))
+
     def timed_copies(do_h2d, do_d2h, reps=3):
+        """Seconds per file of `e2e_files_rank` files' copies issued back to back (H2D on one stream, D2H on another, as
+        the e2e loop keeps them in flight across files): a pipelined conversion cannot be faster than this."""
         best = None
         for _ in range(reps):
             barrier()
             t1 = time.perf_counter()
-            if do_h2d:
-                with torch.cuda.stream(cs[0]):
-                    d_in[0].copy_(th_in, non_blocking=True)
-            if do_d2h:
-                with torch.cuda.stream(cs[1]):
-                    th_out.copy_(d_out[0][:out_bytes], non_blocking=True)
+            for _f in range(e2e_files_rank):
+                if do_h2d:
+                    with torch.cuda.stream(cs[0]):
+                        d_in[0].copy_(th_in, non_blocking=True)
+                if do_d2h:
+                    with torch.cuda.stream(cs[1]):
+                        th_out.copy_(d_out[0][:out_bytes], non_blocking=True)
             torch.cuda.synchronize()
-            dt = allmax(time.perf_counter() - t1)                     # slowest rank
+            dt = allmax(time.perf_counter() - t1) / e2e_files_rank    # slowest rank
             best = dt if best is None else min(best, dt)
         return best
 
     t_h2d, t_d2h, t_both = timed_copies(True, False), timed_copies(False, True), timed_copies(True, True)
-    e2e_files_rank = max(1, max(len(x) for x in shard.assign_files([1] * args.e2e_total_files, world)))
     e2e_file_s = e2e_s / (args.steps * e2e_files_rank)                # per file on the busiest rank
-    ceiling = {"what": "bare pinned cudaMemcpyAsync of one file's payload (H2D) and of its PCM (D2H), ALL ranks at once behind a "
-                       "barrier, slowest rank, best of 3; GB/s are aggregates over the ranks",
+    ceiling = {"what": "bare pinned cudaMemcpyAsync of the payloads (H2D) and PCM (D2H) of as many files per rank as one e2e step "
+                       "converts, issued back to back on two streams, ALL ranks at once behind a barrier, slowest rank, best "
+                       "of 3, per file; GB/s are aggregates over the ranks",
+               "files_per_rank": e2e_files_rank,
                "h2d_only_gbs": world * in_bytes / t_h2d / 1e9, "d2h_only_gbs": world * out_bytes / t_d2h / 1e9,
                "both_h2d_gbs": world * in_bytes / t_both / 1e9, "both_d2h_gbs": world * out_bytes / t_both / 1e9,
                "both_seconds_per_file": t_both, "e2e_seconds_per_file": e2e_file_s, "e2e_over_ceiling": e2e_file_s / t_both}
@@ -430,7 +436,11 @@ def main():
         sm_mhz = clocks["sm_mhz"] or pk.get("sm_max_mhz", 1965.0)
         lds = {"bound": "smem_lut", "what": "shared-memory LUT look-ups (8 B each): the unit that binds this path (SURVEY 8d)",
                "achieved": lookups * 8 / (kernel_ms / 1e3) / 1e9, "peak": lds_peak * 8 / 1e9, "unit": "GB/s",
-               "frac": lookups / (kernel_ms / 1e3) / lds_peak, "traffic": None, "peak_kind": lds_kind,
+               "frac": lookups / (kernel_ms / 1e3) / lds_peak, "traffic": traffic,
+               "traffic_what": "DRAM bytes of one such launch (dram__bytes_read.sum + dram__bytes_write.sum, committed ncu capture of "
+                               "this command: profiles/r02_bench_traffic.json; not re-measured in this run); algorithmic HBM bytes "
+                               "are in roofline_hbm",
+               "peak_kind": lds_kind,
                "lookups_per_launch": lookups, "lookups_per_s": lookups / (kernel_ms / 1e3), "peak_lookups_per_s": lds_peak,
                "kernel_ms": kernel_ms, "files_per_launch": kernel_files,
                "frac_of_nominal_at_observed_clock": lookups / (kernel_ms / 1e3) / (SM_COUNT * LDS_LOOKUPS_PER_CLK_SM * sm_mhz * 1e6)}
@@ -443,7 +453,10 @@ def main():
             "e2e": {"value": e2e_value, "unit": "DSD samples/s", "h2d_bytes_per_step": args.e2e_total_files * in_bytes,
                     "d2h_bytes_per_step": args.e2e_total_files * out_bytes, "files_per_step": args.e2e_total_files,
                     "timer": "wall clock around the synchronous C-ABI calls (d2p_batch_convert_host, pinned host buffers), max over ranks",
-                    "realtime_factor": e2e_value / (2 * 11289600.0), "platform_ceiling": ceiling},
+                    "realtime_factor": e2e_value / (2 * 11289600.0), "platform_ceiling": ceiling,
+                    # the same as scalars (a parser that drops nested objects keeps these)
+                    "ceiling_both_s_per_file": ceiling["both_seconds_per_file"], "over_ceiling": ceiling["e2e_over_ceiling"],
+                    "ceiling_h2d_gbs": ceiling["both_h2d_gbs"], "ceiling_d2h_gbs": ceiling["both_d2h_gbs"]},
             "gpu_launches": int(launches),
             "kernel": "d2p::lutfir_kernel<1,'T',3,1>" if args.dither == "T" else "d2p::lutfir_kernel", "kernel_ms": kernel_ms,
             "roofline": lds, "lds": {"frac": lds["frac"], "achieved": lds["lookups_per_s"], "peak": lds_peak, "unit": "lookups/s",
