@@ -11,7 +11,9 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <future>
 #include <random>
 #include <string>
 #include <vector>
@@ -456,17 +458,22 @@ int d2p_convert_file_ex(const d2p_file_options* opt, const char* in_path, const 
         if (st != D2P_OK) return fail(st);
     } else {
         // WAV / AIFF / AIFC / headerless: the file is streamed through the GPU in 64 MiB slices with bounded pinned memory
-        // (two buffers, whatever the length of the input: a 60-minute 6-channel DSD512 payload is 61 GB).  The streaming
-        // context keeps the filter halo between slices, so the bytes equal the one-pass conversion.
+        // (two input and two output buffers, whatever the length of the input: a 60-minute 6-channel DSD512 payload is
+        // 61 GB).  The streaming context keeps the filter halo between slices, so the bytes equal the one-pass conversion.
+        // Slice n+1 is read from the input file and the PCM of slice n-1 is written to the output file by helper threads
+        // while slice n is on the GPU; D2P_FILE_SERIAL=1 switches the overlap off (for measuring it).
         Bytes h;
         if (opt->out_container != D2P_FILE_RAW && !build_header(opt->out_container, opt->bits, ci.channels, opt->out_rate, frames_max, &h))
             return api_set_error(D2P_ERR_BIT_DEPTH, "Unsupported bit depth");
         const size_t slice = std::max<size_t>(group, ((size_t)64 << 20) / group * group);
         const size_t fb = (size_t)ci.channels * pi.bytes_per_sample, out_cap = ((size_t)48 << 20) / fb * fb + fb;
-        uint8_t* h_in = (uint8_t*)d2p_host_alloc(std::max<size_t>(std::min<uint64_t>(slice, std::max<uint64_t>(linear_bytes, group)), 16));
-        uint8_t* h_out = (uint8_t*)d2p_host_alloc(out_cap);
-        struct Free { uint8_t* a; uint8_t* b; ~Free() { d2p_host_free(a); d2p_host_free(b); } } fr{h_in, h_out};
-        if (!h_in || !h_out) return api_set_error(D2P_ERR_NOMEM, "pinned host allocation failed");
+        const size_t in_cap = std::max<size_t>(std::min<uint64_t>(slice, std::max<uint64_t>(linear_bytes, group)), 16);
+        const char* serial_env = std::getenv("D2P_FILE_SERIAL");
+        const bool overlap = !(serial_env && serial_env[0] == '1') && linear_bytes > slice;   // one slice: nothing to overlap
+        uint8_t* h_in[2] = {(uint8_t*)d2p_host_alloc(in_cap), overlap ? (uint8_t*)d2p_host_alloc(in_cap) : nullptr};
+        uint8_t* h_out[2] = {(uint8_t*)d2p_host_alloc(out_cap), overlap ? (uint8_t*)d2p_host_alloc(out_cap) : nullptr};
+        struct Free { uint8_t** a; uint8_t** b; ~Free() { for (int i = 0; i < 2; ++i) { d2p_host_free(a[i]); d2p_host_free(b[i]); } } } fr{h_in, h_out};
+        if (!h_in[0] || !h_out[0] || (overlap && (!h_in[1] || !h_out[1]))) return api_set_error(D2P_ERR_NOMEM, "pinned host allocation failed");
         d2p_ctx* ctx = nullptr;
         st = d2p_create(&cfg, &ctx);
         if (st != D2P_OK) return st;
@@ -474,31 +481,54 @@ int d2p_convert_file_ex(const d2p_file_options* opt, const char* in_path, const 
         FileCloser of{std::fopen(out_path, "wb")};
         if (!of.f) return api_set_error(D2P_ERR_INVALID_ARG, (std::string("cannot create ") + out_path).c_str());
         if (!h.v.empty() && std::fwrite(h.v.data(), 1, h.v.size(), of.f) != h.v.size()) return fail(api_set_error(D2P_ERR_INVALID_ARG, "write failed"));
+        // declared behind the buffers and files they touch: a pending helper is waited for before those go away
+        std::future<bool> reading, writing;
+        auto settle = [&]() -> bool {                              // true if every helper so far succeeded
+            bool ok = true;
+            if (reading.valid()) ok = reading.get() && ok;
+            if (writing.valid()) ok = writing.get() && ok;
+            return ok;
+        };
+        auto failw = [&](int code) { settle(); return fail(code); };
+        int ob = 0;                                                // output buffer the next pull goes into
         auto drain = [&]() -> int {
             for (;;) {
                 uint64_t n = 0;
-                const int s2 = d2p_pull(ctx, h_out, out_cap, &n);
+                const int s2 = d2p_pull(ctx, h_out[ob], out_cap, &n);
                 if (s2 != D2P_OK) return s2;
                 if (n == 0) return D2P_OK;
-                if (std::fwrite(h_out, fb, (size_t)n, of.f) != (size_t)n) return api_set_error(D2P_ERR_INVALID_ARG, "write failed");
-                frames += n;
+                if (writing.valid() && !writing.get()) return api_set_error(D2P_ERR_INVALID_ARG, "write failed");
+                const uint8_t* src = h_out[ob];
+                FILE* dst = of.f;
+                auto put = [src, dst, fb, n]() { return std::fwrite(src, fb, (size_t)n, dst) == (size_t)n; };
+                if (overlap) { writing = std::async(std::launch::async, put); ob ^= 1; }
+                else if (!put()) return api_set_error(D2P_ERR_INVALID_ARG, "write failed");
+                frames += n;                                       // with the overlap on: handed to the writer
                 if (progress) progress(user, frames, frames_max);
             }
         };
         if (std::fseek(fc.f, (long)ci.data_offset, SEEK_SET) != 0) return fail(api_set_error(D2P_ERR_INVALID_ARG, "short read of the DSD payload"));
+        auto get = [&](uint8_t* dst, size_t n) { FILE* src = fc.f; return [src, dst, n]() { return std::fread(dst, 1, n, src) == n; }; };
+        int ib = 0;
+        if (overlap) reading = std::async(std::launch::async, get(h_in[0], (size_t)std::min<uint64_t>(slice, linear_bytes)));
         for (uint64_t done = 0; done < linear_bytes;) {
-            if (cancel_flag && *cancel_flag) return fail(api_set_error(D2P_ERR_CANCELLED, "conversion cancelled"));
+            if (cancel_flag && *cancel_flag) return failw(api_set_error(D2P_ERR_CANCELLED, "conversion cancelled"));
             const size_t n = (size_t)std::min<uint64_t>(slice, linear_bytes - done);
-            if (std::fread(h_in, 1, n, fc.f) != n) return fail(api_set_error(D2P_ERR_INVALID_ARG, "short read of the DSD payload"));
-            if ((st = d2p_push(ctx, h_in, n)) != D2P_OK || (st = drain()) != D2P_OK) return fail(st);
+            const bool got = overlap ? reading.get() : get(h_in[ib], n)();
+            if (!got) return failw(api_set_error(D2P_ERR_INVALID_ARG, "short read of the DSD payload"));
+            const uint64_t next = std::min<uint64_t>(slice, linear_bytes - done - n);
+            if (overlap && next) reading = std::async(std::launch::async, get(h_in[ib ^ 1], (size_t)next));
+            if ((st = d2p_push(ctx, h_in[ib], n)) != D2P_OK || (st = drain()) != D2P_OK) return failw(st);
             done += n;
+            if (overlap) ib ^= 1;
         }
-        if (cancel_flag && *cancel_flag) return fail(api_set_error(D2P_ERR_CANCELLED, "conversion cancelled"));
+        if (cancel_flag && *cancel_flag) return failw(api_set_error(D2P_ERR_CANCELLED, "conversion cancelled"));
         if (tail) {
-            if (!read_tail(h_in)) return fail(api_set_error(D2P_ERR_INVALID_ARG, "short read of the DSD payload"));
-            if ((st = d2p_push(ctx, h_in, (size_t)(tail * ci.channels))) != D2P_OK) return fail(st);
+            if (!read_tail(h_in[ib])) return failw(api_set_error(D2P_ERR_INVALID_ARG, "short read of the DSD payload"));
+            if ((st = d2p_push(ctx, h_in[ib], (size_t)(tail * ci.channels))) != D2P_OK) return failw(st);
         }
-        if ((st = d2p_finish(ctx)) != D2P_OK || (st = drain()) != D2P_OK) return fail(st);
+        if ((st = d2p_finish(ctx)) != D2P_OK || (st = drain()) != D2P_OK) return failw(st);
+        if (!settle()) return fail(api_set_error(D2P_ERR_INVALID_ARG, "write failed"));
         if (frames != frames_max) return fail(api_set_error(D2P_ERR_STATE, "internal: frame count differs from the plan"));
         int64_t clips = 0;
         if ((st = d2p_stats(ctx, &clips, &R.peak_abs, &R.clipped_samples)) != D2P_OK) return fail(st);

@@ -124,8 +124,12 @@ typedef struct d2p_file_result {
     uint64_t tag_bytes;       /* size of the ID3v2 tag carried over (0: none, unreadable, or copy_tags off) */
 } d2p_file_result;
 
-/* One input file -> one PCM file: parse the container, stream the payload through the GPU
- * (d2p_convert_host: pinned staging, H2D / kernel / D2H overlapped), write header + payload. */
+/* One input file -> one PCM file: parse the container, stream the payload through the GPU, write header + payload.
+ * WAV / AIFF / AIFC / headerless output: 64 MiB slices through a streaming context (d2p_push / d2p_pull) with two
+ * pinned input and two pinned output buffers, whatever the file length; reading slice n+1 and writing the PCM of slice
+ * n-1 overlap with slice n on the GPU, while copy-in, kernel and copy-out of ONE slice run one after the other.
+ * FLAC output: the whole payload and its PCM are held in pinned memory and go through d2p_batch_convert_host
+ * (H2D / kernel / D2H of neighbouring chunks overlapped); the encoder needs the complete stream. */
 int d2p_convert_file(const d2p_file_options* opt, const char* in_path, const char* out_path, d2p_file_result* res);
 /* The same with the reference's cancellation flag and progress report (Rdsd2Pcm::do_conversion(&AtomicBool,
  * Option<Sender<ProgressUpdate>>), rd/lib.rs:275-281): see d2p_batch_set_control.  A cancelled or failed conversion
