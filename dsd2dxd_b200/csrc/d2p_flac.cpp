@@ -15,7 +15,9 @@
 #include <algorithm>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <string>
 #include <thread>
 #include <vector>
@@ -357,7 +359,12 @@ extern "C" int d2p_write_flac_file_ex(const char* path, int bits, int channels, 
     be(0x00, 1); be(34, 3);
     const size_t si = head.size();
     head.insert(head.end(), 34, 0);
-    const std::string vendor = "dsd2pcm_b200";
+    // vendor string in the reference's format, `dsd2dxd v<rdsd2pcm crate version> Unix datetime <seconds>`
+    // (PcmWriter::id3_to_flac_meta, rd/pcm_writer.rs:426-437; the crate is at 0.3.0).  SOURCE_DATE_EPOCH, when set,
+    // replaces the clock so that two runs can give identical files.
+    long long stamp = (long long)std::time(nullptr);
+    if (const char* sde = std::getenv("SOURCE_DATE_EPOCH")) stamp = std::atoll(sde);
+    const std::string vendor = "dsd2dxd v0.3.0 Unix datetime " + std::to_string(stamp);
     size_t vc = 4 + vendor.size() + 4;
     for (int i = 0; i < n_comments; ++i) vc += 4 + std::strlen(comments[i]);
     if (vc >= (1u << 24)) return api_set_error(D2P_ERR_INVALID_ARG, "FLAC: comment block too large");

@@ -6,6 +6,8 @@ is, 20-bit unshifted at bits_per_sample 20, float32 as (clamp(x,-1,1) * 8388607.
 valid stream (sync, frame numbers, CRC-8, CRC-16, STREAMINFO totals and MD5)."""
 import os
 
+import re
+
 import numpy as np
 import pytest
 
@@ -68,7 +70,8 @@ def roundtrip(tmp_path, values, bits, channels, rate, comments=()):
     assert np.array_equal(got, want)
     assert dec["frames"] == (frames + 4095) // 4096
     assert dec["min_frame"] == min(dec["frame_sizes"]) and dec["max_frame"] == max(dec["frame_sizes"])
-    assert dec["vendor"] == "dsd2pcm_b200" and dec["comments"] == list(comments)
+    # the reference's vendor string (rd/pcm_writer.rs:431-436): crate version + the time of writing
+    assert re.fullmatch(r"dsd2dxd v0\.3\.0 Unix datetime \d{9,}", dec["vendor"]) and dec["comments"] == list(comments)
     return raw, dec
 
 

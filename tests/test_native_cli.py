@@ -108,6 +108,42 @@ def test_cli_stdin_block_pushes_match_oracle(cli, ref_files, rel, flags, kw):
 
 
 @pytest.mark.gpu
+def test_cli_output_directories_and_stdin_to_a_container(cli, ref_files, tmp_path):
+    """derive_output_dir (rd/conversion_context.rs:447-477): with -p the input's directory, relative to the base directory
+    (src/main.rs:262-273: the parent of the inputs' longest common path), is re-created under the output directory.
+    stdin with a container output is written as output[_<rate>].<ext> (:418-425, convert_stdin src/main.rs:316-346)."""
+    a, b = tmp_path / "lib" / "artist" / "one", tmp_path / "lib" / "artist" / "two"
+    a.mkdir(parents=True); b.mkdir(parents=True)
+    raw = open(ref_files["test/1kHz_stereo_128.dsf"], "rb").read()
+    (a / "x.dsf").write_bytes(raw); (b / "y.dsf").write_bytes(raw)
+    out = tmp_path / "out"
+    r = subprocess.run([cli, "-o", "W", "-r", "176400", "-b", "24", "-d", "X", "-p", str(out), str(a / "x.dsf"), str(b / "y.dsf")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    # common path lib/artist, base directory lib: outputs land in out/artist/one and out/artist/two
+    x, y = out / "artist" / "one" / "x.wav", out / "artist" / "two" / "y.wav"
+    assert x.exists() and y.exists() and x.read_bytes() == y.read_bytes()
+    # a single input: base directory = its own directory, so the file sits directly in -p
+    out1 = tmp_path / "out1"
+    r = subprocess.run([cli, "-o", "W", "-r", "176400", "-b", "24", "-d", "X", "-a", "-p", str(out1), str(a / "x.dsf")], capture_output=True, text=True)
+    assert r.returncode == 0 and (out1 / "x_176_4K.wav").read_bytes() == x.read_bytes()
+    # stdin -> WAV in -p, and in the working directory without -p
+    dsd = open(ref_files["test/1kHz_stereo_i.dsd"], "rb").read()
+    flags = ["-c", "2", "-f", "I", "-e", "M", "-r", "352800", "-b", "24", "-d", "X"]
+    ref = orclib.convert(np.frombuffer(dsd, dtype=np.uint8), channels=2, layout="I", lsb_first=False, dsd_rate=1, out_rate=352800,
+                         bits=24, stdout_mode=False, want_f64=False)
+    r = subprocess.run([cli] + flags + ["-o", "W", "-a", "-p", str(out), "-"], input=dsd, capture_output=True)
+    assert r.returncode == 0, r.stderr.decode()
+    assert (out / "output_352_8K.wav").read_bytes() == orc.WRITERS["W"](ref.planar, 24, 352800)
+    assert not list(out.glob("*.tmp"))
+    cwd = tmp_path / "cwd"
+    cwd.mkdir()
+    r = subprocess.run([cli] + flags + ["-o", "A", "-"], input=dsd, capture_output=True, cwd=cwd)
+    assert r.returncode == 0, r.stderr.decode()
+    assert (cwd / "output.aif").read_bytes() == orc.WRITERS["A"](ref.planar, 24, 352800)
+
+
+@pytest.mark.gpu
 def test_cancel_flag_and_progress_callback(tmp_path):
     raw = np.random.default_rng(5).integers(0, 256, size=2 * 4096 * 60000, dtype=np.uint8)      # 8 chunks of 64 MiB
     cfg = d2p.make_config(dsd_rate=4, out_rate=352800, bits=24, channels=2)
@@ -207,4 +243,12 @@ def test_convert_file_streams_long_files_in_bounded_slices(tmp_path):
     assert res["frames"] == ref.frames[0]
     assert (tmp_path / "o.wav").read_bytes() == orc.WRITERS["W"](ref.planar, 24, 176400)
     assert len(seen) >= 3 and seen[-1] == (ref.frames[0], ref.frames[0]) and all(a[0] < b[0] for a, b in zip(seen, seen[1:]))
+    # the reader / writer helpers that overlap neighbouring slices change nothing but the timing
+    os.environ["D2P_FILE_SERIAL"] = "1"
+    try:
+        d2p.convert_file(src, tmp_path / "serial.wav", out_rate=176400, bits=24, container="W", raw_channels=2, raw_layout="P",
+                         raw_lsb_first=True, raw_dsd_rate=4)
+    finally:
+        del os.environ["D2P_FILE_SERIAL"]
+    assert (tmp_path / "serial.wav").read_bytes() == (tmp_path / "o.wav").read_bytes()
     assert res["peak_abs"] == np.abs(orclib.convert(raw, dsd_rate=4, out_rate=176400, bits=24, channels=2).f64 * (1 << 23)).max()

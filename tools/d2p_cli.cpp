@@ -104,20 +104,65 @@ static const char* rate_suffix(unsigned rate) {       // abbrev_rate_pair, rd/co
     }
 }
 
-static std::string out_name(const Cli& c, const std::string& in) {   // get_out_filename_path :400-440
-    const char* ext = c.output == 'W' ? "wav" : c.output == 'A' ? "aif" : c.output == 'C' ? "aifc" : c.output == 'F' ? "flac" : "out";
-    std::string dir, stem = "output";
-    if (in != "-") {
-        const size_t slash = in.find_last_of('/');
-        dir = slash == std::string::npos ? "" : in.substr(0, slash + 1);
-        stem = slash == std::string::npos ? in : in.substr(slash + 1);
-        const size_t dot = stem.find_last_of('.');
-        if (dot != std::string::npos && dot > 0) stem = stem.substr(0, dot);
+// Base directory of main() (src/main.rs:262-273): one input -> its parent; several -> the parent of their longest
+// common path.  Inputs are canonicalised first, as the reference does.
+static std::filesystem::path base_dir_of(const std::vector<std::string>& files) {
+    namespace fs = std::filesystem;
+    std::vector<fs::path> paths;
+    std::error_code ec;
+    for (const std::string& f : files) {
+        if (f == "-") continue;
+        fs::path p = fs::canonical(f, ec);
+        if (!ec) paths.push_back(p);
     }
-    if (!c.out_dir.empty()) dir = c.out_dir + "/";
-    std::string name = dir + stem;
+    if (paths.empty()) return fs::path("/");
+    if (paths.size() == 1) return paths[0].has_parent_path() ? paths[0].parent_path() : fs::path("/");
+    fs::path common;
+    for (auto it = paths[0].begin(); it != paths[0].end(); ++it) {
+        const fs::path cand = common / *it;
+        bool all = true;
+        for (const fs::path& q : paths) {
+            auto a = cand.begin(); auto b = q.begin();
+            for (; a != cand.end() && b != q.end() && *a == *b; ++a, ++b) {}
+            if (a != cand.end()) { all = false; break; }
+        }
+        if (!all) break;
+        common = cand;
+    }
+    if (common.empty()) common = "/";
+    return common.has_parent_path() && common != common.root_path() ? common.parent_path() : fs::path("/");
+}
+
+// get_out_filename_path (rd/conversion_context.rs:400-445) + derive_output_dir (:447-477): <stem>[_<rate>].<ext>, in the
+// input's directory, or with -p in <outdir>/<input directory relative to the base directory> (created when missing);
+// stdin: "output[_<rate>].<ext>" in <outdir> or the working directory.
+static std::string out_name(const Cli& c, const std::string& in, const std::filesystem::path& base_dir) {
+    namespace fs = std::filesystem;
+    const char* ext = c.output == 'W' ? "wav" : c.output == 'A' ? "aif" : c.output == 'C' ? "aifc" : c.output == 'F' ? "flac" : "out";
+    std::string stem = "output";
+    fs::path dir;
+    std::error_code ec;
+    if (in == "-") {
+        if (!c.out_dir.empty()) dir = c.out_dir;
+    } else {
+        fs::path full = fs::canonical(in, ec);
+        if (ec) full = fs::absolute(in);
+        if (full.has_stem()) stem = full.stem().string();
+        const fs::path parent = full.parent_path();
+        if (c.out_dir.empty()) {
+            const size_t slash = in.find_last_of('/');                 // as given on the command line
+            dir = slash == std::string::npos ? "" : in.substr(0, slash);
+            if (slash == 0) dir = "/";
+        } else {
+            const fs::path rel = parent.lexically_relative(base_dir);
+            const bool inside = !rel.empty() && *rel.begin() != "..";
+            dir = fs::path(c.out_dir) / (inside ? (rel == "." ? fs::path() : rel) : parent);   // strip_prefix(..).unwrap_or(parent)
+        }
+    }
+    if (!c.out_dir.empty() && !fs::exists(dir, ec)) fs::create_directories(dir, ec);
+    std::string name = stem;
     if (c.append && rate_suffix(c.rate)) name += std::string("_") + rate_suffix(c.rate);
-    return name + "." + ext;
+    return (dir / (name + "." + ext)).string();
 }
 
 // copy_artwork (rd/conversion_context.rs:479-533): with -p, every .jpg / .jpeg / .png of the input's directory is copied
@@ -147,6 +192,42 @@ static void report(const Cli& c, const std::string& file, double audio_s, double
 
 static double now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
+// stdin -> container file "output[_<rate>].<ext>" (convert_stdin src/main.rs:316-346, file name :418-425; the reference's
+// run_all_tests.sh does `-o w -p out . -`).  A container header needs the frame count before the first sample: stdin is
+// spooled to a temporary raw file beside the output and converted like any headerless input, in bounded memory.
+static int run_stdin_to_file(const Cli& c, char dither) {
+    namespace fs = std::filesystem;
+    const std::string out = out_name(c, "-", fs::path("/"));
+    const std::string spool = out + ".stdin.tmp";
+    struct Rm { const std::string& p; ~Rm() { std::error_code ec; std::filesystem::remove(p, ec); } } rm{spool};
+    unsigned long long bytes = 0;
+    {
+        std::FILE* f = std::fopen(spool.c_str(), "wb");
+        if (!f) { std::fprintf(stderr, "d2p_cli: cannot create %s\n", spool.c_str()); return 1; }
+        std::vector<uint8_t> buf((size_t)4 << 20);
+        size_t n;
+        bool ok = true;
+        while (!g_cancel && (n = std::fread(buf.data(), 1, buf.size(), stdin)) > 0) { ok = std::fwrite(buf.data(), 1, n, f) == n; bytes += n; if (!ok) break; }
+        ok = std::fclose(f) == 0 && ok;
+        if (!ok) { std::fprintf(stderr, "d2p_cli: write failed: %s\n", spool.c_str()); return 1; }
+        if (g_cancel) { std::fprintf(stderr, "d2p_cli: cancelled\n"); return 1; }
+    }
+    d2p_file_options o;
+    std::memset(&o, 0, sizeof o);
+    o.out_rate = c.rate; o.filter = c.filter; o.bits = c.bits; o.dither = dither; o.level_db = c.level; o.out_container = c.output;
+    o.dither_seed = c.seed; o.device = c.device;
+    o.raw_channels = c.channels; o.raw_layout = c.format; o.raw_lsb_first = c.endian == 'L'; o.raw_dsd_rate = c.in_rate;
+    o.raw_block_size = c.block;
+    d2p_file_result r;
+    const double t0 = now();
+    const int st = d2p_convert_file_ex(&o, spool.c_str(), out.c_str(), &r, &g_cancel, nullptr, nullptr);
+    const double dt = now() - t0;
+    if (st != D2P_OK) { std::fprintf(stderr, "d2p_cli: stdin: %s\n", st == D2P_ERR_CANCELLED ? "cancelled" : d2p_last_error()); return 1; }
+    report(c, "stdin", (double)bytes / c.channels * 8.0 / (2822400.0 * c.in_rate), dt, dt);
+    if (!c.quiet && r.clipped_samples) std::fprintf(stderr, "%lld samples clipped\n", (long long)r.clipped_samples);
+    return 0;
+}
+
 // stdin -> stdout through d2p_push / d2p_pull, one reader block group per call (process_blocks)
 static int run_stdin(const Cli& c, char dither) {
     d2p_config cfg;
@@ -154,7 +235,7 @@ static int run_stdin(const Cli& c, char dither) {
     cfg.dsd_rate = c.in_rate; cfg.out_rate = c.rate; cfg.filter = c.filter; cfg.bits = c.bits; cfg.dither = dither;
     cfg.channels = c.channels; cfg.level_db = c.level; cfg.in_layout = c.format; cfg.lsb_first = c.endian == 'L';
     cfg.block_size = c.block; cfg.out_format = D2P_OUT_INTERLEAVED_LE; cfg.dither_seed = c.seed; cfg.device = c.device;
-    if (c.output != 'S') { std::fprintf(stderr, "d2p_cli: stdin input writes headerless PCM to stdout (-o S)\n"); return 2; }
+    if (c.output != 'S') return run_stdin_to_file(c, dither);
     d2p_plan_info pi;
     d2p_ctx* ctx = nullptr;
     int st = d2p_plan(&cfg, &pi);
@@ -211,6 +292,7 @@ int main(int argc, char** argv) {
     std::signal(SIGINT, on_sigint);
     if (d2p_device_count() < 1) { std::fprintf(stderr, "d2p_cli: no CUDA device (the library has no CPU path)\n"); return 1; }
     int failed = 0;
+    const std::filesystem::path base_dir = base_dir_of(c.files);
     for (const std::string& f : c.files) {
         if (f == "-") { failed += run_stdin(c, dither) != 0; continue; }
         d2p_file_options o;
@@ -223,7 +305,7 @@ int main(int argc, char** argv) {
         o.copy_tags = 1;                        // the reference always carries a readable tag over (save_output :565-590)
         o.append_rate = c.append ? 1 : 0;
         d2p_file_result r;
-        const std::string out = c.output == 'S' ? "/dev/stdout" : out_name(c, f);
+        const std::string out = c.output == 'S' ? "/dev/stdout" : out_name(c, f, base_dir);
         const double t0 = now();
         const int st = d2p_convert_file_ex(&o, f.c_str(), out.c_str(), &r, &g_cancel, nullptr, nullptr);
         const double dt = now() - t0;
