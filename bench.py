@@ -206,7 +206,8 @@ def smem_reads(info, in_bytes_per_ch, channels, frames):
     return channels * reads
 
 
-def time_paths(args, d2p, torch, dev, lds_peak):
+def time_paths(args, d2p, torch, dev, lds_peak, check=True):
+    import numpy as np
     out = []
     stream = torch.cuda.current_stream().cuda_stream
     gen = torch.Generator(device=dev)
@@ -232,11 +233,20 @@ def time_paths(args, d2p, torch, dev, lds_peak):
             ts.append(a.elapsed_time(b))
         batch.close()
         ms = sorted(ts)[len(ts) // 2]
+        # the timed output against the oracle on the first seconds (causal filters: a prefix of the input gives a prefix
+        # of the output; block groups / interleaved frames both put the first pre * ch bytes of the payload first)
+        prefix_equal, pre_s = None, min(2.0, args.path_seconds)
+        if check:
+            from oracle import orclib
+            pre = int(pre_s * 2822400 * rate / 8) // 4096 * 4096
+            ref = orclib.convert(d_in[:pre * ch].cpu().numpy(), want_f64=False, dither="X", **kw)
+            prefix_equal = bool(ref.pcm.size > 0 and np.array_equal(d_out[:ref.pcm.size].cpu().numpy(), ref.pcm))
         reads = smem_reads(info, per_ch, ch, frames)
         out.append({"config": name, "workload": f"{args.path_seconds:g} s of {what}, device-resident, dither X",
                     "kernel": "d2p::lutfir_kernel" if info["num_stages"] == 1 else "d2p::lm_kernel", "kernel_ms": ms,
                     "dsd_samples_per_s": per_ch * 8 * ch / (ms / 1e3), "realtime_factor": args.path_seconds / (ms / 1e3),
-                    "smem_reads_8B": reads, "lds_frac": reads / (ms / 1e3) / lds_peak})
+                    "smem_reads_8B": reads, "lds_frac": reads / (ms / 1e3) / lds_peak, "seconds": args.path_seconds, "dither": "X",
+                    "oracle_prefix_equal": prefix_equal, "oracle_prefix_seconds": pre_s if check else None})
         del d_in, d_out
     return out
 
